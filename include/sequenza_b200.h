@@ -1,0 +1,175 @@
+/*
+ * sequenza_b200.h -- C ABI of libsequenza_b200.so, the B200 (sm_100a) implementation of
+ * sequenza 3.0.0's cellularity x ploidy likelihood path.
+ *
+ * The reference is pure R and has no FFI boundary of its own; these entry points are
+ * the narrowest cuts through R/bayes.R that keep every R-visible behaviour (see
+ * INTEGRATION.md for the .Call shim and the R-side edits).  Paths below are relative to
+ * the reference tree.
+ *
+ * Conventions
+ *   - Every function returns 0 (SQZ_OK) or a negative SQZ_ERR_* code; the message is
+ *     available from sqz_last_error() (thread-local).  Nothing aborts the process.
+ *   - All vectors are fp64.  Inputs are read-only.  Per-segment / per-position vectors
+ *     all have length N (the R caller recycles scalars, as data.frame() does at
+ *     R/bayes.R:43-45 and :130-131).  NA_real_ and NaN are both "NA" on input
+ *     (is.na()); NA on output carries R's NA_real_ bit pattern 0x7FF00000000007A2.
+ *   - Matrices are column-major, as in R.
+ *   - priors.table is passed as two parallel vectors prior_CN / prior_value of length
+ *     n_prior (R/bayes.R:55-59: later rows override earlier ones; values are divided by
+ *     their sum over all type rows).
+ *   - "host" entry points take host pointers and do their own transfers; "_dev" entry
+ *     points take device pointers valid on the CURRENT device plus a caller-owned
+ *     workspace and a cudaStream_t (passed as void*), and are asynchronous.
+ *   - CNt_max - CNt_min + 1 <= 64.
+ */
+#ifndef SEQUENZA_B200_H
+#define SEQUENZA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SQZ_OK 0
+#define SQZ_ERR_ARG (-1)    /* bad argument (R: stop()) */
+#define SQZ_ERR_CUDA (-2)   /* CUDA runtime failure; see sqz_last_error() */
+#define SQZ_ERR_NOGPU (-3)  /* no usable device */
+#define SQZ_ERR_SIZE (-4)   /* size beyond a stated limit */
+
+/* grid evaluation mode */
+#define SQZ_MODE_FAST 0     /* factorised product kernel + faithful repair of flagged points */
+#define SQZ_MODE_FAITHFUL 1 /* every (grid point, segment, type) through the nmath sequence */
+
+const char* sqz_version(void);
+const char* sqz_last_error(void);
+int sqz_device_count(void);
+/* Frees every cached per-device buffer and stream held by the host entry points. */
+int sqz_release(void);
+
+/* ---------------------------------------------------------------------------------
+ * B1  baf.model.fit grid -- replaces fit.cp + pblapply, R/bayes.R:109-115.
+ * lpp_sum_out[ic * nP + ip] = sum(baf.bayes(cellularity[ic], ploidy[ip], ...)[, 4]),
+ * i.e. result$LPP in expand.grid(ploidy, cellularity) order (R/bayes.R:106-107, :116).
+ * The tapply / LogSumLik / exp steps (R/bayes.R:117-123) stay in R.
+ * n_gpus >= 1: cellularity columns are split over that many devices of this process.
+ * --------------------------------------------------------------------------------- */
+int sqz_baf_grid(const double* Bf, const double* depth_ratio, const double* sd_Bf,
+                 const double* sd_ratio, const double* weight_Bf,
+                 const double* weight_ratio, int64_t N, const double* ploidy, int64_t nP,
+                 const double* cellularity, int64_t nC, double avg_depth_ratio,
+                 int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                 const double* prior_value, int n_prior, int ratio_priority, int n_gpus,
+                 int mode, double* lpp_sum_out);
+
+/* Cohort form of B1 (BASELINE config 5): S samples share one grid.  Sample k owns
+ * segments seg_offsets[k] .. seg_offsets[k+1]-1 of the concatenated vectors and
+ * avg_depth_ratio[k]; lpp_sum_out is S x (nC*nP), sample-major.  One launch per device. */
+int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
+                       const double* depth_ratio, const double* sd_Bf,
+                       const double* sd_ratio, const double* weight_Bf,
+                       const double* weight_ratio, const double* ploidy, int64_t nP,
+                       const double* cellularity, int64_t nC,
+                       const double* avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                       const double* prior_CN, const double* prior_value, int n_prior,
+                       int ratio_priority, int n_gpus, int mode, double* lpp_sum_out);
+
+/* Device-resident form of B1 for callers that own device memory (one process per GPU,
+ * torch.distributed): segment vectors, seg_offsets (S+1 int64) and avg_depth_ratio (S)
+ * are DEVICE pointers; ploidy / cellularity / priors are HOST pointers (they
+ * parameterise the launch).  Evaluates cellularity columns ic0 <= ic < ic1 only and
+ * writes S x ((ic1-ic0)*nP) doubles to d_lpp_sum_out (device).  workspace must hold
+ * sqz_baf_grid_workspace_bytes(...) bytes, 256-byte aligned. */
+size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard);
+int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
+                     const double* d_Bf, const double* d_depth_ratio,
+                     const double* d_sd_Bf, const double* d_sd_ratio,
+                     const double* d_weight_Bf, const double* d_weight_ratio,
+                     const double* ploidy, int64_t nP, const double* cellularity,
+                     int64_t nC, int64_t ic0, int64_t ic1, const double* d_avg_depth_ratio,
+                     int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                     const double* prior_value, int n_prior, int ratio_priority, int mode,
+                     void* workspace, size_t workspace_bytes, void* stream,
+                     double* d_lpp_sum_out);
+
+/* ---------------------------------------------------------------------------------
+ * B2  baf.bayes at one (cellularity, ploidy) -- replaces R/bayes.R:46-98.
+ * out is N x 4 column-major: CNt, A, B, LPP (R/bayes.R:99).  Callers: R/results.R:128,
+ * :139, R/graphics.R:419.  Rows whose posterior is NaN for every type (the reference
+ * stops with an R error there) come back as NA, NA, NA, NaN.
+ * --------------------------------------------------------------------------------- */
+int sqz_baf_point(const double* Bf, const double* depth_ratio, const double* sd_Bf,
+                  const double* sd_ratio, const double* weight_Bf,
+                  const double* weight_ratio, int64_t N, double cellularity, double ploidy,
+                  double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                  const double* prior_CN, const double* prior_value, int n_prior,
+                  int ratio_priority, double* out);
+int sqz_baf_point_dev(const double* d_Bf, const double* d_depth_ratio,
+                      const double* d_sd_Bf, const double* d_sd_ratio,
+                      const double* d_weight_Bf, const double* d_weight_ratio, int64_t N,
+                      double cellularity, double ploidy, double avg_depth_ratio,
+                      int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                      const double* prior_value, int n_prior, int ratio_priority,
+                      void* stream, double* d_out);
+
+/* ---------------------------------------------------------------------------------
+ * B3  mufreq.bayes at one (cellularity, ploidy) -- replaces R/bayes.R:132-170.
+ * out is N x 4 column-major: CNn, CNt, Mt, LPP (R/bayes.R:171).  Callers:
+ * R/results.R:153, :161.  weight_* have length N.
+ * --------------------------------------------------------------------------------- */
+int sqz_mufreq_point(const double* mufreq, const double* depth_ratio,
+                     const double* weight_mufreq, const double* weight_ratio, int64_t N,
+                     double cellularity, double ploidy, double avg_depth_ratio,
+                     int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                     const double* prior_value, int n_prior, double* out);
+int sqz_mufreq_point_dev(const double* d_mufreq, const double* d_depth_ratio,
+                         const double* d_weight_mufreq, const double* d_weight_ratio,
+                         int64_t N, double cellularity, double ploidy,
+                         double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                         const double* prior_CN, const double* prior_value, int n_prior,
+                         void* stream, double* d_out);
+
+/* ---------------------------------------------------------------------------------
+ * B4  mufreq.model.fit grid -- replaces fit.cp + pblapply, R/bayes.R:179-185.
+ * Same output convention as sqz_baf_grid.
+ * --------------------------------------------------------------------------------- */
+int sqz_mufreq_grid(const double* mufreq, const double* depth_ratio,
+                    const double* weight_mufreq, const double* weight_ratio, int64_t N,
+                    const double* ploidy, int64_t nP, const double* cellularity,
+                    int64_t nC, double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                    const double* prior_CN, const double* prior_value, int n_prior,
+                    int n_gpus, double* lpp_sum_out);
+int sqz_mufreq_grid_dev(const double* d_mufreq, const double* d_depth_ratio,
+                        const double* d_weight_mufreq, const double* d_weight_ratio,
+                        int64_t N, const double* ploidy, int64_t nP,
+                        const double* cellularity, int64_t nC, int64_t ic0, int64_t ic1,
+                        double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                        const double* prior_CN, const double* prior_value, int n_prior,
+                        void* workspace, size_t workspace_bytes, void* stream,
+                        double* d_lpp_sum_out);
+size_t sqz_mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nC_shard);
+
+/* ---------------------------------------------------------------------------------
+ * Model points as the kernels compute them (R/model.R:49-67), for checking the device
+ * arithmetic against tests/testthat/test.model.R.  out is T x 5 column-major:
+ * CNt, second index (B or Mt), model depth.ratio, model BAF or mufreq, normalised prior.
+ * kind 0 = baf types (R/model.R:22-37), 1 = mufreq types (R/model.R:39-47).
+ * Returns T through *T_out; out may be NULL to query T.
+ * --------------------------------------------------------------------------------- */
+int sqz_model_points(int kind, double cellularity, double ploidy, double avg_depth_ratio,
+                     int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                     const double* prior_value, int n_prior, int* T_out, double* out);
+
+/* ---------------------------------------------------------------------------------
+ * Measured fp64 issue rate of the current device, for the roofline denominator that
+ * MEASURED_PEAKS.json does not carry: dependent-free DFMA chains on every SM.
+ * tflops_out = 2 * DFMA / s / 1e12.  No counterpart in the reference.
+ * --------------------------------------------------------------------------------- */
+int sqz_fp64_peak(int device, int repeats, double* tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEQUENZA_B200_H */

@@ -1,0 +1,479 @@
+// sqz_api.cu -- extern "C" surface of libsequenza_b200.so (see include/sequenza_b200.h).
+//
+// Host entry points stage R-owned host vectors into cached per-device buffers, run the
+// kernels on a private stream per device and copy each device's slice of the result
+// straight into the caller's output (no device-to-device gather: the consumer is the
+// R process).  The _dev entry points are thin argument checks over the launchers.
+#include <mutex>
+#include <vector>
+
+#include "sqz_common.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+
+// launchers (sqz_baf_grid.cu, sqz_mufreq.cu)
+size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs);
+int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
+                    const double* d_ratio, const double* d_sdBf, const double* d_sdr,
+                    const double* d_wBf, const double* d_wr, const double* h_ploidy,
+                    int64_t nP, const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1,
+                    const double* d_adr, int CNt_min, int CNt_max, int CNn,
+                    const double* prior_CN, const double* prior_value, int n_prior,
+                    int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
+                    cudaStream_t st, double* d_out);
+int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_sdBf,
+                     const double* d_sdr, const double* d_wBf, const double* d_wr, int64_t N,
+                     double cellularity, double ploidy, double adr, int CNt_min, int CNt_max,
+                     int CNn, const double* prior_CN, const double* prior_value, int n_prior,
+                     int ratio_priority, cudaStream_t st, double* d_out);
+size_t mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nCs);
+int mufreq_point_launch(const double* d_F, const double* d_ratio, const double* d_wm,
+                        const double* d_wr, int64_t N, double cellularity, double ploidy,
+                        double adr, int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                        const double* prior_value, int n_prior, cudaStream_t st,
+                        double* d_out);
+int mufreq_grid_launch(const double* d_F, const double* d_ratio, const double* d_wm,
+                       const double* d_wr, int64_t N, const double* h_ploidy, int64_t nP,
+                       const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1, double adr,
+                       int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                       const double* prior_value, int n_prior, void* workspace,
+                       size_t workspace_bytes, cudaStream_t st, double* d_out);
+int model_points_launch(int kind, double cellularity, double ploidy, double adr, int CNt_min,
+                        int CNt_max, int CNn, const double* prior_CN,
+                        const double* prior_value, int n_prior, int* T_out, double* h_out);
+
+// ---- per-device cache used by the host entry points --------------------------------
+struct DevCtx {
+  bool live = false;
+  cudaStream_t st = nullptr;
+  void* in = nullptr;   // staged inputs
+  size_t in_cap = 0;
+  void* ws = nullptr;   // kernel workspace
+  size_t ws_cap = 0;
+  void* out = nullptr;  // result slice
+  size_t out_cap = 0;
+};
+static std::mutex g_mu;
+static std::vector<DevCtx> g_ctx;
+
+static int grow(void** p, size_t* cap, size_t need) {
+  if (need <= *cap) return SQZ_OK;
+  if (*p) SQZ_CUDA(cudaFree(*p));
+  *p = nullptr;
+  *cap = 0;
+  size_t want = need + need / 4 + 256;
+  SQZ_CUDA(cudaMalloc(p, want));
+  *cap = want;
+  return SQZ_OK;
+}
+
+static int ctx_for(int dev, DevCtx** out) {
+  if ((int)g_ctx.size() <= dev) g_ctx.resize(dev + 1);
+  DevCtx& c = g_ctx[dev];
+  SQZ_CUDA(cudaSetDevice(dev));
+  if (!c.live) {
+    SQZ_CUDA(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+    c.live = true;
+  }
+  *out = &c;
+  return SQZ_OK;
+}
+
+static int usable_devices(int n_gpus, int* ndev) {
+  int have = 0;
+  cudaError_t e = cudaGetDeviceCount(&have);
+  if (e != cudaSuccess || have < 1) {
+    cudaGetLastError();
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  }
+  if (n_gpus < 1) return fail(SQZ_ERR_ARG, "n_gpus must be >= 1");
+  *ndev = n_gpus < have ? n_gpus : have;
+  return SQZ_OK;
+}
+
+static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() { cudaGetDevice(&prev); }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const vec[6],
+                         const double* ploidy, int64_t nP, const double* cell, int64_t nC,
+                         const double* adr, int CNt_min, int CNt_max, int CNn,
+                         const double* prior_CN, const double* prior_value, int n_prior,
+                         int ratio_priority, int n_gpus, int mode, double* out) {
+  if (S < 0 || nP < 0 || nC < 0) return fail(SQZ_ERR_ARG, "negative size");
+  if (S > 0 && !seg_off) return fail(SQZ_ERR_ARG, "seg_offsets is null");
+  const int64_t N = S > 0 ? seg_off[S] : 0;
+  if (S > 0 && seg_off[0] != 0) return fail(SQZ_ERR_ARG, "seg_offsets[0] must be 0");
+  for (int64_t k = 0; k < S; ++k)
+    if (seg_off[k + 1] < seg_off[k]) return fail(SQZ_ERR_ARG, "seg_offsets must be non-decreasing");
+  for (int k = 0; k < 6; ++k)
+    if (N > 0 && !vec[k]) return fail(SQZ_ERR_ARG, "a per-segment vector is null");
+  if ((nP > 0 && !ploidy) || (nC > 0 && !cell) || (S > 0 && !adr) || (S * nP * nC > 0 && !out))
+    return fail(SQZ_ERR_ARG, "null pointer argument");
+  if (S == 0 || nP == 0 || nC == 0) return SQZ_OK;
+  int ndev = 0;
+  int rc = usable_devices(n_gpus, &ndev);
+  if (rc) return rc;
+  if (ndev > nC) ndev = (int)nC;
+  std::lock_guard<std::mutex> lk(g_mu);
+  DeviceGuard guard;
+  const int64_t G = nP * nC;
+  // contiguous blocks of cellularity columns per device
+  std::vector<int64_t> c0(ndev + 1);
+  for (int d = 0; d <= ndev; ++d) c0[d] = nC * d / ndev;
+  for (int d = 0; d < ndev; ++d) {
+    DevCtx* c;
+    if ((rc = ctx_for(d, &c))) return rc;
+    const int64_t nCs = c0[d + 1] - c0[d];
+    const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
+    const size_t in_need = 6 * vbytes + a256((size_t)(S + 1) * 8) + a256((size_t)S * 8);
+    if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
+    const size_t ws_need = baf_grid_workspace_bytes(N, S, nP, nCs);
+    if ((rc = grow(&c->ws, &c->ws_cap, ws_need))) return rc;
+    if ((rc = grow(&c->out, &c->out_cap, (size_t)(S * nCs * nP) * 8))) return rc;
+    char* p = (char*)c->in;
+    const double* dv[6];
+    for (int k = 0; k < 6; ++k) {
+      dv[k] = (const double*)p;
+      if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, vec[k], (size_t)N * 8, cudaMemcpyHostToDevice, c->st));
+      p += vbytes;
+    }
+    int64_t* d_off = (int64_t*)p;
+    SQZ_CUDA(cudaMemcpyAsync(d_off, seg_off, (size_t)(S + 1) * 8, cudaMemcpyHostToDevice, c->st));
+    p += a256((size_t)(S + 1) * 8);
+    double* d_adr = (double*)p;
+    SQZ_CUDA(cudaMemcpyAsync(d_adr, adr, (size_t)S * 8, cudaMemcpyHostToDevice, c->st));
+    rc = baf_grid_launch(S, d_off, N, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], ploidy, nP,
+                         cell, nC, c0[d], c0[d + 1], d_adr, CNt_min, CNt_max, CNn, prior_CN,
+                         prior_value, n_prior, ratio_priority, mode, c->ws, c->ws_cap, c->st,
+                         (double*)c->out);
+    if (rc) return rc;
+    // device slice [S][nCs*nP] -> host [S][G] at column offset c0*nP
+    SQZ_CUDA(cudaMemcpy2DAsync(out + c0[d] * nP, (size_t)G * 8, c->out, (size_t)(nCs * nP) * 8,
+                               (size_t)(nCs * nP) * 8, (size_t)S, cudaMemcpyDeviceToHost,
+                               c->st));
+  }
+  for (int d = 0; d < ndev; ++d) {
+    SQZ_CUDA(cudaSetDevice(d));
+    SQZ_CUDA(cudaStreamSynchronize(g_ctx[d].st));
+  }
+  return SQZ_OK;
+}
+
+// ---- fp64 issue-rate probe -----------------------------------------------------------
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double seed) {
+  double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4,
+         a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 0.999999, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+    a0 = fma(a0, m, c);
+    a1 = fma(a1, m, c);
+    a2 = fma(a2, m, c);
+    a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c);
+    a5 = fma(a5, m, c);
+    a6 = fma(a6, m, c);
+    a7 = fma(a7, m, c);
+  }
+  double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+  if (r == 12345.678) out[0] = r;  // keeps the chains alive
+}
+
+// single-device host wrapper shared by the point entry points: stage k vectors of
+// length N, run `launch`, copy N x 4 back.
+template <class F>
+static int point_host(int k, const double* const* vec, int64_t N, double* out, F launch) {
+  if (N < 0) return fail(SQZ_ERR_ARG, "negative N");
+  for (int i = 0; i < k; ++i)
+    if (N > 0 && !vec[i]) return fail(SQZ_ERR_ARG, "a per-row vector is null");
+  if (N > 0 && !out) return fail(SQZ_ERR_ARG, "out is null");
+  int ndev = 0;
+  int rc = usable_devices(1, &ndev);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_mu);
+  int cur = 0;
+  SQZ_CUDA(cudaGetDevice(&cur));
+  DevCtx* c;
+  if ((rc = ctx_for(cur, &c))) return rc;
+  const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
+  if ((rc = grow(&c->in, &c->in_cap, k * vbytes))) return rc;
+  if ((rc = grow(&c->out, &c->out_cap, (size_t)(N > 0 ? N : 1) * 32))) return rc;
+  const double* dv[8];
+  char* p = (char*)c->in;
+  for (int i = 0; i < k; ++i) {
+    dv[i] = (const double*)p;
+    if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, vec[i], (size_t)N * 8, cudaMemcpyHostToDevice, c->st));
+    p += vbytes;
+  }
+  rc = launch(dv, c->st, (double*)c->out);
+  if (rc) return rc;
+  if (N > 0)
+    SQZ_CUDA(cudaMemcpyAsync(out, c->out, (size_t)N * 32, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaStreamSynchronize(c->st));
+  return SQZ_OK;
+}
+
+}  // namespace sqz
+
+using namespace sqz;
+
+extern "C" {
+
+const char* sqz_version(void) { return "sequenza_b200 0.1.0 (sm_100a)"; }
+const char* sqz_last_error(void) { return g_err.c_str(); }
+
+int sqz_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int sqz_release(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  DeviceGuard guard;
+  for (size_t d = 0; d < g_ctx.size(); ++d) {
+    DevCtx& c = g_ctx[d];
+    if (!c.live) continue;
+    cudaSetDevice((int)d);
+    cudaStreamSynchronize(c.st);
+    if (c.in) cudaFree(c.in);
+    if (c.ws) cudaFree(c.ws);
+    if (c.out) cudaFree(c.out);
+    cudaStreamDestroy(c.st);
+    c = DevCtx();
+  }
+  return SQZ_OK;
+}
+
+int sqz_baf_grid(const double* Bf, const double* depth_ratio, const double* sd_Bf,
+                 const double* sd_ratio, const double* weight_Bf, const double* weight_ratio,
+                 int64_t N, const double* ploidy, int64_t nP, const double* cellularity,
+                 int64_t nC, double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                 const double* prior_CN, const double* prior_value, int n_prior,
+                 int ratio_priority, int n_gpus, int mode, double* lpp_sum_out) {
+  if (N < 0) return fail(SQZ_ERR_ARG, "negative N");
+  const int64_t off[2] = {0, N};
+  const double* vec[6] = {Bf, depth_ratio, sd_Bf, sd_ratio, weight_Bf, weight_ratio};
+  return baf_grid_host(1, off, vec, ploidy, nP, cellularity, nC, &avg_depth_ratio, CNt_min,
+                       CNt_max, CNn, prior_CN, prior_value, n_prior, ratio_priority, n_gpus,
+                       mode, lpp_sum_out);
+}
+
+int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
+                       const double* depth_ratio, const double* sd_Bf, const double* sd_ratio,
+                       const double* weight_Bf, const double* weight_ratio,
+                       const double* ploidy, int64_t nP, const double* cellularity,
+                       int64_t nC, const double* avg_depth_ratio, int CNt_min, int CNt_max,
+                       int CNn, const double* prior_CN, const double* prior_value,
+                       int n_prior, int ratio_priority, int n_gpus, int mode,
+                       double* lpp_sum_out) {
+  const double* vec[6] = {Bf, depth_ratio, sd_Bf, sd_ratio, weight_Bf, weight_ratio};
+  return baf_grid_host(S, seg_offsets, vec, ploidy, nP, cellularity, nC, avg_depth_ratio,
+                       CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, ratio_priority,
+                       n_gpus, mode, lpp_sum_out);
+}
+
+size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard) {
+  return baf_grid_workspace_bytes(N_total, S, nP, nC_shard);
+}
+
+int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
+                     const double* d_Bf, const double* d_depth_ratio, const double* d_sd_Bf,
+                     const double* d_sd_ratio, const double* d_weight_Bf,
+                     const double* d_weight_ratio, const double* ploidy, int64_t nP,
+                     const double* cellularity, int64_t nC, int64_t ic0, int64_t ic1,
+                     const double* d_avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                     const double* prior_CN, const double* prior_value, int n_prior,
+                     int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
+                     void* stream, double* d_lpp_sum_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return baf_grid_launch(S, d_seg_offsets, N_total, d_Bf, d_depth_ratio, d_sd_Bf, d_sd_ratio,
+                         d_weight_Bf, d_weight_ratio, ploidy, nP, cellularity, nC, ic0, ic1,
+                         d_avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
+                         n_prior, ratio_priority, mode, workspace, workspace_bytes,
+                         (cudaStream_t)stream, d_lpp_sum_out);
+}
+
+int sqz_baf_point(const double* Bf, const double* depth_ratio, const double* sd_Bf,
+                  const double* sd_ratio, const double* weight_Bf, const double* weight_ratio,
+                  int64_t N, double cellularity, double ploidy, double avg_depth_ratio,
+                  int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                  const double* prior_value, int n_prior, int ratio_priority, double* out) {
+  const double* vec[6] = {Bf, depth_ratio, sd_Bf, sd_ratio, weight_Bf, weight_ratio};
+  return point_host(6, vec, N, out, [&](const double** dv, cudaStream_t st, double* d_out) {
+    return baf_point_launch(dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], N, cellularity, ploidy,
+                            avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
+                            n_prior, ratio_priority, st, d_out);
+  });
+}
+
+int sqz_baf_point_dev(const double* d_Bf, const double* d_depth_ratio, const double* d_sd_Bf,
+                      const double* d_sd_ratio, const double* d_weight_Bf,
+                      const double* d_weight_ratio, int64_t N, double cellularity,
+                      double ploidy, double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                      const double* prior_CN, const double* prior_value, int n_prior,
+                      int ratio_priority, void* stream, double* d_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return baf_point_launch(d_Bf, d_depth_ratio, d_sd_Bf, d_sd_ratio, d_weight_Bf,
+                          d_weight_ratio, N, cellularity, ploidy, avg_depth_ratio, CNt_min,
+                          CNt_max, CNn, prior_CN, prior_value, n_prior, ratio_priority,
+                          (cudaStream_t)stream, d_out);
+}
+
+int sqz_mufreq_point(const double* mufreq, const double* depth_ratio,
+                     const double* weight_mufreq, const double* weight_ratio, int64_t N,
+                     double cellularity, double ploidy, double avg_depth_ratio, int CNt_min,
+                     int CNt_max, int CNn, const double* prior_CN, const double* prior_value,
+                     int n_prior, double* out) {
+  const double* vec[4] = {mufreq, depth_ratio, weight_mufreq, weight_ratio};
+  return point_host(4, vec, N, out, [&](const double** dv, cudaStream_t st, double* d_out) {
+    return mufreq_point_launch(dv[0], dv[1], dv[2], dv[3], N, cellularity, ploidy,
+                               avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
+                               n_prior, st, d_out);
+  });
+}
+
+int sqz_mufreq_point_dev(const double* d_mufreq, const double* d_depth_ratio,
+                         const double* d_weight_mufreq, const double* d_weight_ratio,
+                         int64_t N, double cellularity, double ploidy, double avg_depth_ratio,
+                         int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                         const double* prior_value, int n_prior, void* stream, double* d_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return mufreq_point_launch(d_mufreq, d_depth_ratio, d_weight_mufreq, d_weight_ratio, N,
+                             cellularity, ploidy, avg_depth_ratio, CNt_min, CNt_max, CNn,
+                             prior_CN, prior_value, n_prior, (cudaStream_t)stream, d_out);
+}
+
+size_t sqz_mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nC_shard) {
+  return mufreq_grid_workspace_bytes(N, nP, nC_shard);
+}
+
+int sqz_mufreq_grid_dev(const double* d_mufreq, const double* d_depth_ratio,
+                        const double* d_weight_mufreq, const double* d_weight_ratio, int64_t N,
+                        const double* ploidy, int64_t nP, const double* cellularity,
+                        int64_t nC, int64_t ic0, int64_t ic1, double avg_depth_ratio,
+                        int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                        const double* prior_value, int n_prior, void* workspace,
+                        size_t workspace_bytes, void* stream, double* d_lpp_sum_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return mufreq_grid_launch(d_mufreq, d_depth_ratio, d_weight_mufreq, d_weight_ratio, N,
+                            ploidy, nP, cellularity, nC, ic0, ic1, avg_depth_ratio, CNt_min,
+                            CNt_max, CNn, prior_CN, prior_value, n_prior, workspace,
+                            workspace_bytes, (cudaStream_t)stream, d_lpp_sum_out);
+}
+
+int sqz_mufreq_grid(const double* mufreq, const double* depth_ratio,
+                    const double* weight_mufreq, const double* weight_ratio, int64_t N,
+                    const double* ploidy, int64_t nP, const double* cellularity, int64_t nC,
+                    double avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                    const double* prior_CN, const double* prior_value, int n_prior,
+                    int n_gpus, double* lpp_sum_out) {
+  if (N < 0 || nP < 0 || nC < 0) return fail(SQZ_ERR_ARG, "negative size");
+  const double* vec[4] = {mufreq, depth_ratio, weight_mufreq, weight_ratio};
+  for (int k = 0; k < 4; ++k)
+    if (N > 0 && !vec[k]) return fail(SQZ_ERR_ARG, "a per-position vector is null");
+  if ((nP > 0 && !ploidy) || (nC > 0 && !cellularity) || (nP * nC > 0 && !lpp_sum_out))
+    return fail(SQZ_ERR_ARG, "null pointer argument");
+  if (nP == 0 || nC == 0) return SQZ_OK;
+  int ndev = 0;
+  int rc = usable_devices(n_gpus, &ndev);
+  if (rc) return rc;
+  if (ndev > nC) ndev = (int)nC;
+  std::lock_guard<std::mutex> lk(g_mu);
+  DeviceGuard guard;
+  std::vector<int64_t> c0(ndev + 1);
+  for (int d = 0; d <= ndev; ++d) c0[d] = nC * d / ndev;
+  for (int d = 0; d < ndev; ++d) {
+    DevCtx* c;
+    if ((rc = ctx_for(d, &c))) return rc;
+    const int64_t nCs = c0[d + 1] - c0[d];
+    const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
+    if ((rc = grow(&c->in, &c->in_cap, 4 * vbytes))) return rc;
+    if ((rc = grow(&c->ws, &c->ws_cap, mufreq_grid_workspace_bytes(N, nP, nCs)))) return rc;
+    if ((rc = grow(&c->out, &c->out_cap, (size_t)(nCs * nP) * 8))) return rc;
+    char* p = (char*)c->in;
+    const double* dv[4];
+    for (int k = 0; k < 4; ++k) {
+      dv[k] = (const double*)p;
+      if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, vec[k], (size_t)N * 8, cudaMemcpyHostToDevice, c->st));
+      p += vbytes;
+    }
+    rc = mufreq_grid_launch(dv[0], dv[1], dv[2], dv[3], N, ploidy, nP, cellularity, nC, c0[d],
+                            c0[d + 1], avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN,
+                            prior_value, n_prior, c->ws, c->ws_cap, c->st, (double*)c->out);
+    if (rc) return rc;
+    SQZ_CUDA(cudaMemcpyAsync(lpp_sum_out + c0[d] * nP, c->out, (size_t)(nCs * nP) * 8,
+                             cudaMemcpyDeviceToHost, c->st));
+  }
+  for (int d = 0; d < ndev; ++d) {
+    SQZ_CUDA(cudaSetDevice(d));
+    SQZ_CUDA(cudaStreamSynchronize(g_ctx[d].st));
+  }
+  return SQZ_OK;
+}
+
+int sqz_model_points(int kind, double cellularity, double ploidy, double avg_depth_ratio,
+                     int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                     const double* prior_value, int n_prior, int* T_out, double* out) {
+  if (out && sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return model_points_launch(kind, cellularity, ploidy, avg_depth_ratio, CNt_min, CNt_max,
+                             CNn, prior_CN, prior_value, n_prior, T_out, out);
+}
+
+int sqz_fp64_peak(int device, int repeats, double* tflops_out) {
+  if (!tflops_out) return fail(SQZ_ERR_ARG, "tflops_out is null");
+  int ndev = 0;
+  int rc = usable_devices(1, &ndev);
+  if (rc) return rc;
+  DeviceGuard guard;
+  SQZ_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  SQZ_CUDA(cudaGetDeviceProperties(&prop, device));
+  double* d = nullptr;
+  SQZ_CUDA(cudaMalloc(&d, 8));
+  cudaEvent_t e0, e1;
+  SQZ_CUDA(cudaEventCreate(&e0));
+  SQZ_CUDA(cudaEventCreate(&e1));
+  const int iters = 1 << 15, blocks = prop.multiProcessorCount * 8, threads = 256;
+  if (repeats < 1) repeats = 1;
+  double best = 0;
+  for (int r = 0; r < repeats + 1; ++r) {
+    SQZ_CUDA(cudaEventRecord(e0));
+    fp64_peak_kernel<<<blocks, threads>>>(d, iters, 1.0);
+    SQZ_CUDA(cudaEventRecord(e1));
+    SQZ_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    SQZ_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    double tf = 2.0 * 8 * (double)iters * blocks * threads / (ms * 1e-3) / 1e12;
+    if (r > 0 && tf > best) best = tf;  // first launch is warm-up
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *tflops_out = best;
+  return SQZ_OK;
+}
+
+}  // extern "C"

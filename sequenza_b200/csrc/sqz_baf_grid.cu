@@ -1,0 +1,670 @@
+// sqz_baf_grid.cu -- baf.model.fit grid search (R/bayes.R:103-116 over R/bayes.R:38-101)
+// and baf.bayes at one grid point, hand-written for sm_100a.
+//
+// What the reference does per grid point g = (cellularity c, ploidy p) and segment s:
+//   post[t] = dt((log mr[t] - log r_s)/sr_s, 5, log) + log prior[t]
+//           + dt((mb[t] - Bf_s)/sb_s, 5, log)                     t = (CNt, B) rows
+//   LPP[g] += max_t post[t]                                       (R/bayes.R:61-79, :112)
+//
+// Fast path (SQZ_MODE_FAST).  With df = 5,  dt(x, 5, log) = k5 - 3 log(1 + x^2/5), so
+//   max_t post[t] = 2 k5 - 3 log( min_t (1 + xr_t^2/5) (1 + xb_t^2/5) prior_t^(-1/3) ).
+// Three exact factorisations make this cheap:
+//   (1) xr depends on the type only through CNt and xb does not depend on ploidy, so
+//       min_t = min_CNt [ (1 + xr^2/5) * w_CNt * min_B (1 + xb^2/5) ] and the inner
+//       min over B is shared by every ploidy of a cellularity column;
+//   (2) sum_s log q_s = log prod_s q_s: the per-segment minima are multiplied into a
+//       running product whose binary exponent is peeled off into an integer every four
+//       segments, so the main loop has no log at all;
+//   (3) the segment-size weights enter through sr_s = sd/sqrt(w) only.
+// One CTA owns one cellularity, a tile of PT ploidies and one chunk of a sample's
+// segments; every thread streams segments (two coalesced 16-byte loads each,
+// prefetched one iteration ahead) and keeps PT running products in registers.
+// Anything non-finite (NaN model points at cellularity 1, zero sd, overflow) makes the
+// product Inf/NaN, which flags that grid point; flagged points are recomputed by the
+// faithful kernel below, which walks the nmath dt() sequence type by type.
+#include "sqz_common.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+struct BafGridArgs {
+  int64_t S;
+  const int64_t* seg_off;  // [S+1]
+  const double *Bf, *ratio, *sdBf, *sdr, *wBf, *wr;  // raw per-segment vectors
+  const double2* rk;  // fast path: (kr, er)   xr/sqrt5 = fma(log mr, kr, er)
+  const double2* bk;  // fast path: (kb, eb)   xb/sqrt5 = fma(mb, kb, eb)
+  const int* nB;      // [S] segments that carry a BAF term
+  const double* adr;  // [S] avg.depth.ratio
+  const double* ploidy;  // [nP]
+  const double* cell;    // [nCs] this shard's cellularities
+  int nP, nCs, nPT, nChunk;
+  int rp;
+  double t5;
+};
+
+// ---- per-segment preparation for the fast path ------------------------------------
+__global__ void baf_prep_kernel(BafGridArgs a, double2* rk, double2* bk, int* nB) {
+  const int64_t smp = blockIdx.y;
+  const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
+  const double inv_sqrt5 = 0.44721359549995793928;
+  int cnt = 0;
+  for (int64_t s = s0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < s1;
+       s += (int64_t)gridDim.x * blockDim.x) {
+    double sr = a.sdr[s] / sqrt(a.wr[s]);
+    double kr = (1.0 / sr) * inv_sqrt5;
+    double lr = log(a.ratio[s]);
+    double Bf = a.Bf[s];
+    double sb = a.sdBf[s] / sqrt(a.wBf[s]);
+    bool hasB = !isnan(Bf) && !isnan(sb);  // R/bayes.R:68-69
+    double kb = 0., eb = 0.;
+    if (hasB) {
+      kb = (1.0 / sb) * inv_sqrt5;
+      eb = -(Bf * kb);
+    }
+    rk[s] = make_double2(kr, -(lr * kr));
+    bk[s] = make_double2(kb, eb);
+    cnt += hasB ? 1 : 0;
+  }
+  // block-wide count, one atomic per CTA
+  __shared__ int sh;
+  if (threadIdx.x == 0) sh = 0;
+  __syncthreads();
+  for (int off = 16; off; off >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&sh, cnt);
+  __syncthreads();
+  if (threadIdx.x == 0 && sh) atomicAdd(&nB[smp], sh);
+}
+
+// ---- fast grid kernel ---------------------------------------------------------------
+template <int PT, bool RP>
+__global__ void __launch_bounds__(256)
+baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
+                     long long* __restrict__ partE) {
+  extern __shared__ double sm[];
+  double* lmr = sm;                 // [nc][PT] log model depth ratio
+  double* mb = sm + m.nc * PT;      // [T] model BAF, type order
+  __shared__ double redM[8][PT];
+  __shared__ long long redE[8][PT];
+  __shared__ unsigned redBad[8];
+
+  int64_t b = blockIdx.x;
+  const int pt = (int)(b % a.nPT);
+  b /= a.nPT;
+  const int ic = (int)(b % a.nCs);
+  b /= a.nCs;
+  const int chunk = (int)(b % a.nChunk);
+  const int64_t smp = b / a.nChunk;
+  const int p0 = pt * PT;
+  const int tid = threadIdx.x;
+
+  // model tables for this (cellularity, ploidy tile): R/model.R:1-14 via R/model.R:49-56
+  const double cell = a.cell[ic];
+  const double adr = a.adr[smp];
+  for (int i = tid; i < m.nc * PT; i += blockDim.x) {
+    int c = i / PT, j = i - c * PT;
+    int ip = min(p0 + j, a.nP - 1);  // ragged last tile repeats the last ploidy
+    lmr[i] = log(theoretical_depth_ratio((double)(m.CNt_min + c), cell, a.ploidy[ip],
+                                         (double)m.CNn, adr));
+  }
+  for (int t = tid; t < m.T; t += blockDim.x) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    mb[t] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+                            (double)m.CNn);
+  }
+  __syncthreads();
+
+  const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
+  const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
+  const int64_t cb = s0 + (int64_t)chunk * per;
+  const int64_t ce = min(cb + per, s1);
+
+  double P[PT];
+  int E[PT];
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    P[j] = 1.0;
+    E[j] = 0;
+  }
+  unsigned bad = 0;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+
+  auto renorm = [&]() {
+#pragma unroll
+    for (int j = 0; j < PT; ++j) {
+      int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+      // not a positive normal number (Inf, NaN, zero, denormal, negative): flag
+      if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+      E[j] += (hi >> 20) - 1023;
+      P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+    }
+  };
+
+  int64_t s = cb + tid;
+  double2 rk_n = make_double2(0., 0.), bk_n = rk_n;
+  if (s < ce) {
+    rk_n = a.rk[s];
+    bk_n = a.bk[s];
+  }
+  int it = 0;
+  while (s < ce) {
+    const double2 rk = rk_n, bk = bk_n;
+    const int64_t sn = s + blockDim.x;
+    if (sn < ce) {  // prefetch the next segment of this thread
+      rk_n = a.rk[sn];
+      bk_n = a.bk[sn];
+    }
+    double qmin[PT];
+    double sel[RP ? PT : 1];
+#pragma unroll
+    for (int j = 0; j < PT; ++j) qmin[j] = INF;
+    if (RP) {
+#pragma unroll
+      for (int j = 0; j < (RP ? PT : 1); ++j) sel[j] = 1.0;
+    }
+    int t = 0;
+    for (int c = 0; c < m.nc; ++c) {
+      // min over B of |xb| (first strict minimum; NaN never wins): R/bayes.R:70-72
+      const int tend = m.toff[c + 1];
+      double mabs = INF;
+      for (; t < tend; ++t) {
+        double ax = fabs(fma(mb[t], bk.x, bk.y));
+        if (ax < mabs) mabs = ax;
+      }
+      const double u = fma(mabs, mabs, 1.0);  // 1 + xb^2/5
+      const double wc = m.w[c];
+      const double wub = u * wc;
+      const double* l = lmr + c * PT;
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        double x = fma(l[j], rk.x, rk.y);
+        double tt = fma(x, x, 1.0);  // 1 + xr^2/5
+        if (!RP) {
+          double q = tt * wub;
+          if (q < qmin[j]) qmin[j] = q;
+        } else {
+          // ratio.priority: CNt chosen on the ratio score alone (R/bayes.R:81-88)
+          double ar = tt * wc;
+          if (ar < qmin[j]) {
+            qmin[j] = ar;
+            sel[RP ? j : 0] = u;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PT; ++j) P[j] *= RP ? qmin[j] * sel[RP ? j : 0] : qmin[j];
+    if ((++it & 3) == 0) renorm();
+    s = sn;
+  }
+  renorm();
+
+  // CTA reduction: sum of log(mantissa) (each in [0, log 2)), exact integer exponents
+  const int lane = tid & 31, warp = tid >> 5, nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    double v = log(P[j]);
+    long long e = E[j];
+    for (int off = 16; off; off >>= 1) {
+      v += __shfl_xor_sync(0xffffffffu, v, off);
+      e += __shfl_xor_sync(0xffffffffu, e, off);
+    }
+    if (lane == 0) {
+      redM[warp][j] = v;
+      redE[warp][j] = e;
+    }
+  }
+  for (int off = 16; off; off >>= 1) bad |= __shfl_xor_sync(0xffffffffu, bad, off);
+  if (lane == 0) redBad[warp] = bad;
+  __syncthreads();
+  if (tid < PT && p0 + tid < a.nP) {
+    double v = 0.;
+    long long e = 0;
+    unsigned bd = 0;
+    for (int w = 0; w < nwarp; ++w) {
+      v += redM[w][tid];
+      e += redE[w][tid];
+      bd |= redBad[w];
+    }
+    if ((bd >> tid) & 1u) v = __longlong_as_double(0x7FF8000000000000LL);
+    const int64_t Gs = (int64_t)a.nCs * a.nP;
+    const int64_t o = ((int64_t)chunk * a.S + smp) * Gs + (int64_t)ic * a.nP + p0 + tid;
+    partM[o] = v;
+    partE[o] = e;
+  }
+}
+
+// ---- finalize: LPP[g] = (n + nB) k5 - 3 (E ln2 + M) in double-double ----------------
+__global__ void baf_grid_finalize_kernel(BafGridArgs a, const double* __restrict__ partM,
+                                         const long long* __restrict__ partE,
+                                         double* __restrict__ out, int* __restrict__ fix_list,
+                                         int* __restrict__ fix_count) {
+  const int64_t Gs = (int64_t)a.nCs * a.nP;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.S * Gs) return;
+  const int64_t smp = i / Gs;
+  double M = 0.;
+  long long E = 0;
+  for (int ch = 0; ch < a.nChunk; ++ch) {
+    M += partM[(int64_t)ch * a.S * Gs + i];
+    E += partE[(int64_t)ch * a.S * Gs + i];
+  }
+  const double n = (double)(a.seg_off[smp + 1] - a.seg_off[smp]);
+  const double Kn = n + (double)a.nB[smp];
+  const double k5 = a.t5 - SQZ_LN_SQRT_2PI;
+  const double ln2_hi = 0.693147180559945286, ln2_lo = 2.319046813846299558e-17;
+  const double Ed = (double)E;
+  // p1 + e1 = Kn * k5
+  double p1 = Kn * k5, e1 = fma(Kn, k5, -p1);
+  // L + eL = E * ln2
+  double L = Ed * ln2_hi, eL = fma(Ed, ln2_hi, -L) + Ed * ln2_lo;
+  // s + es = L + M
+  double sL = L + M, bb = sL - L;
+  double es = ((L - (sL - bb)) + (M - bb)) + eL;
+  // p3 + e3 = 3 (s + es)
+  double p3 = 3.0 * sL, e3 = fma(3.0, sL, -p3) + 3.0 * es;
+  double r = p1 - p3, b2 = r - p1;
+  double er = ((p1 - (r - b2)) + (-p3 - b2)) + (e1 - e3);
+  double res = r + er;
+  if (n == 0) res = 0.;
+  out[i] = res;
+  if (isnan(res)) {
+    int k = atomicAdd(fix_count, 1);
+    fix_list[k] = (int)i;
+  }
+}
+
+// ---- faithful evaluation of one segment at one grid point (R/bayes.R:61-94) -------
+// lratio[c] = log(model depth.ratio) per copy number, baf[t] per type row.
+// Returns the winning copy-number index kc (-1: every posterior NaN) and B.
+__device__ __forceinline__ void baf_eval_faithful(const CnModel& m, const double* lratio,
+                                                  const double* baf, double Bf, double lr,
+                                                  double sdBf, double sdr, double wBf,
+                                                  double wr, int rp, double t5, int& kc,
+                                                  int& kb, double& lpp) {
+  const double sr = sdr / sqrt(wr);
+  const double sb = sdBf / sqrt(wBf);
+  const bool hasB = !isnan(Bf) && !isnan(sb);
+  kc = -1;
+  kb = 0;
+  double best = 0.;
+  if (!rp) {
+    for (int c = 0; c < m.nc; ++c) {
+      const double scr = dt5_log((lratio[c] - lr) / sr, t5) + m.lprior[c];
+      for (int t = m.toff[c]; t < m.toff[c + 1]; ++t) {
+        const double post = hasB ? scr + dt5_log((baf[t] - Bf) / sb, t5) : scr;
+        if (!isnan(post) && (kc < 0 || post > best)) {  // which.max: first, NaN skipped
+          best = post;
+          kc = c;
+          kb = t - m.toff[c];
+        }
+      }
+    }
+  } else {
+    int kr = -1;
+    double bests = 0.;
+    for (int c = 0; c < m.nc; ++c) {
+      const double scr = dt5_log((lratio[c] - lr) / sr, t5) + m.lprior[c];
+      if (!isnan(scr) && (kr < 0 || scr > bests)) {
+        bests = scr;
+        kr = c;
+      }
+    }
+    if (kr >= 0) {
+      for (int t = m.toff[kr]; t < m.toff[kr + 1]; ++t) {
+        const double post = hasB ? bests + dt5_log((baf[t] - Bf) / sb, t5) : bests;
+        if (!isnan(post) && (kc < 0 || post > best)) {
+          best = post;
+          kc = kr;
+          kb = t - m.toff[kr];
+        }
+      }
+    }
+  }
+  lpp = (kc < 0) ? __longlong_as_double(0x7FF8000000000000LL) : best;
+}
+
+__device__ __forceinline__ void build_point_model(const CnModel& m, double cell,
+                                                  double ploidy, double adr,
+                                                  double* lratio, double* baf) {
+  for (int c = threadIdx.x; c < m.nc; c += blockDim.x)
+    lratio[c] = log(theoretical_depth_ratio((double)(m.CNt_min + c), cell, ploidy,
+                                            (double)m.CNn, adr));
+  for (int t = threadIdx.x; t < m.T; t += blockDim.x) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    baf[t] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+                             (double)m.CNn);
+  }
+}
+
+// Faithful grid kernel: persistent CTAs walk a list of (sample, grid point) items --
+// either the points the fast path flagged (fix_list / fix_count) or, when fix_list is
+// null, every point (SQZ_MODE_FAITHFUL).
+__global__ void __launch_bounds__(256)
+baf_grid_faithful_kernel(BafGridArgs a, CnModel m, const int* __restrict__ fix_list,
+                         const int* __restrict__ fix_count, double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* lratio = sm;       // [nc]
+  double* baf = sm + m.nc;   // [T]
+  __shared__ double red[3][8];
+  const int64_t Gs = (int64_t)a.nCs * a.nP;
+  const int64_t n_items = fix_list ? (int64_t)*fix_count : a.S * Gs;
+  for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int64_t i = fix_list ? (int64_t)fix_list[item] : item;
+    const int64_t smp = i / Gs, g = i - smp * Gs;
+    const int ic = (int)(g / a.nP), ip = (int)(g - (int64_t)ic * a.nP);
+    __syncthreads();
+    build_point_model(m, a.cell[ic], a.ploidy[ip], a.adr[smp], lratio, baf);
+    __syncthreads();
+    DD acc = dd_zero();
+    for (int64_t s = a.seg_off[smp] + threadIdx.x; s < a.seg_off[smp + 1];
+         s += blockDim.x) {
+      int kc, kb;
+      double lpp;
+      baf_eval_faithful(m, lratio, baf, a.Bf[s], log(a.ratio[s]), a.sdBf[s], a.sdr[s],
+                        a.wBf[s], a.wr[s], a.rp, a.t5, kc, kb, lpp);
+      dd_add(acc, lpp);  // R sum(): no na.rm (R/bayes.R:112)
+    }
+    // CTA reduction in double-double, fixed order
+    for (int off = 16; off; off >>= 1) {
+      DD o;
+      o.hi = __shfl_xor_sync(0xffffffffu, acc.hi, off);
+      o.lo = __shfl_xor_sync(0xffffffffu, acc.lo, off);
+      o.special = __shfl_xor_sync(0xffffffffu, acc.special, off);
+      dd_merge(acc, o);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+      red[0][warp] = acc.hi;
+      red[1][warp] = acc.lo;
+      red[2][warp] = acc.special;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      DD tot = dd_zero();
+      for (int w = 0; w < (int)((blockDim.x + 31) >> 5); ++w) {
+        DD o{red[0][w], red[1][w], red[2][w]};
+        dd_merge(tot, o);
+      }
+      out[i] = dd_value(tot);
+    }
+  }
+}
+
+// ---- baf.bayes at one grid point: one thread per segment, N x 4 column-major -----
+__global__ void __launch_bounds__(256)
+baf_point_kernel(int64_t N, const double* Bf, const double* ratio, const double* sdBf,
+                 const double* sdr, const double* wBf, const double* wr, double cell,
+                 double ploidy, double adr, CnModel m, int rp, double t5,
+                 double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* lratio = sm;
+  double* baf = sm + m.nc;
+  build_point_model(m, cell, ploidy, adr, lratio, baf);
+  __syncthreads();
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < N;
+       s += (int64_t)gridDim.x * blockDim.x) {
+    int kc, kb;
+    double lpp;
+    const double bf = Bf[s];
+    baf_eval_faithful(m, lratio, baf, bf, log(ratio[s]), sdBf[s], sdr[s], wBf[s], wr[s],
+                      rp, t5, kc, kb, lpp);
+    double cn = na_real(), A = na_real(), B = na_real();
+    if (kc >= 0) {
+      cn = (double)(m.CNt_min + kc);
+      B = (double)kb;
+      A = cn - B;
+      if (isnan(bf)) A = B = na_real();  // R/bayes.R:90-92
+    }
+    out[s] = cn;
+    out[N + s] = A;
+    out[2 * N + s] = B;
+    out[3 * N + s] = lpp;
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------
+int build_cn_model(int kind, int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                   const double* prior_value, int n_prior, CnModel* m, bool* fast_ok) {
+  if (CNt_min < 0 || CNt_max < CNt_min) return fail(SQZ_ERR_ARG, "need 0 <= CNt.min <= CNt.max");
+  if (CNt_max - CNt_min + 1 > kMaxCN)
+    return fail(SQZ_ERR_SIZE, "CNt.max - CNt.min + 1 exceeds 64 copy numbers");
+  if (CNn < 1) return fail(SQZ_ERR_ARG, "CNn must be >= 1");
+  if (n_prior < 0 || (n_prior > 0 && (!prior_CN || !prior_value)))
+    return fail(SQZ_ERR_ARG, "priors.table pointers missing");
+  m->CNt_min = CNt_min;
+  m->nc = CNt_max - CNt_min + 1;
+  m->CNn = CNn;
+  int T = 0;
+  double v[kMaxCN];
+  long double psum = 0.0L;
+  bool ok = true;
+  for (int c = 0; c < m->nc; ++c) {
+    int cn = CNt_min + c;
+    int rows = kind == 0 ? (CNn < 2 ? 1 : cn / 2 + 1) : cn + 1;
+    m->toff[c] = T;
+    T += rows;
+    v[c] = 1.0;
+    for (int i = 0; i < n_prior; ++i)
+      if ((double)cn == prior_CN[i]) v[c] = prior_value[i];  // R/bayes.R:56-58
+    psum += (long double)v[c] * rows;
+  }
+  m->toff[m->nc] = T;
+  m->T = T;
+  for (int c = m->nc + 1; c <= kMaxCN; ++c) m->toff[c] = T;
+  for (int c = 0; c < kMaxCN; ++c) {
+    if (c < m->nc) {
+      m->prior[c] = v[c] / (double)psum;  // R/bayes.R:59
+      m->lprior[c] = log(m->prior[c]);
+      m->w[c] = cbrt(1.0 / m->prior[c]);
+      if (!(m->prior[c] >= 0.0) || !isfinite(m->prior[c])) ok = false;
+    } else {
+      m->prior[c] = m->lprior[c] = m->w[c] = 0.;
+    }
+  }
+  if (fast_ok) *fast_ok = ok && CNn >= 2;
+  return SQZ_OK;
+}
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct GridPlan {
+  int PT, nPT, nChunk, threads;
+};
+
+static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
+                          const CnModel* m) {
+  GridPlan g;
+  const int cand[3] = {8, 16, 32};
+  double bestc = 0;
+  g.PT = 32;
+  const int nc = m ? m->nc : 8, T = m ? m->T : 20;
+  for (int k = 0; k < 3; ++k) {
+    int pt = cand[k];
+    double cost = (double)((nP + pt - 1) / pt) * (pt * (4.0 * nc + 1) + 2.0 * T + 2.0 * nc);
+    if (k == 0 || cost < bestc) {
+      bestc = cost;
+      g.PT = pt;
+    }
+  }
+  g.nPT = (int)((nP + g.PT - 1) / g.PT);
+  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+  g.threads = avg > 1024 ? 256 : (avg > 64 ? 128 : 64);
+  const int64_t base = S * nCs * g.nPT;
+  int64_t want = base > 0 ? (148 * 2 * 3 + base - 1) / base : 1;  // ~3 waves of 2 CTAs/SM
+  int64_t cap = avg / ((int64_t)g.threads * 8);
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  if (want > 64) want = 64;
+  g.nChunk = (int)want;
+  return g;
+}
+
+struct Workspace {
+  double2 *rk, *bk;
+  int* nB;
+  double *ploidy, *cell;
+  double* partM;
+  long long* partE;
+  int *fix_list, *fix_count;
+  size_t bytes;
+};
+
+static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
+  // partials are sized for the largest chunk count the planner can pick
+  Workspace w;
+  size_t off = 0;
+  char* p = (char*)base;
+  auto take = [&](size_t bytes) {
+    void* r = p ? (void*)(p + off) : nullptr;
+    off += align256(bytes);
+    return r;
+  };
+  const size_t n = (size_t)(N_total > 0 ? N_total : 1);
+  const size_t items = (size_t)(S * nCs * nP > 0 ? S * nCs * nP : 1);
+  // nChunk depends on nPT (PT); bound it for any PT the planner may choose
+  int64_t base_min = S * nCs * ((nP + 31) / 32);
+  int64_t want = base_min > 0 ? (148 * 2 * 3 + base_min - 1) / base_min : 1;
+  if (want > 64) want = 64;
+  if (want < 1) want = 1;
+  w.rk = (double2*)take(n * sizeof(double2));
+  w.bk = (double2*)take(n * sizeof(double2));
+  w.nB = (int*)take((size_t)(S > 0 ? S : 1) * sizeof(int));
+  w.ploidy = (double*)take((size_t)(nP > 0 ? nP : 1) * sizeof(double));
+  w.cell = (double*)take((size_t)(nCs > 0 ? nCs : 1) * sizeof(double));
+  w.partM = (double*)take(items * (size_t)want * sizeof(double));
+  w.partE = (long long*)take(items * (size_t)want * sizeof(long long));
+  w.fix_list = (int*)take(items * sizeof(int));
+  w.fix_count = (int*)take(sizeof(int));
+  w.bytes = off;
+  return w;
+}
+
+size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
+  return carve(nullptr, N_total, S, nP, nCs).bytes;
+}
+
+int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
+                    const double* d_ratio, const double* d_sdBf, const double* d_sdr,
+                    const double* d_wBf, const double* d_wr, const double* h_ploidy,
+                    int64_t nP, const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1,
+                    const double* d_adr, int CNt_min, int CNt_max, int CNn,
+                    const double* prior_CN, const double* prior_value, int n_prior,
+                    int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
+                    cudaStream_t st, double* d_out) {
+  if (S < 0 || N_total < 0 || nP < 0 || nC < 0 || ic0 < 0 || ic1 > nC || ic0 > ic1)
+    return fail(SQZ_ERR_ARG, "negative size or bad cellularity shard");
+  if (mode != SQZ_MODE_FAST && mode != SQZ_MODE_FAITHFUL)
+    return fail(SQZ_ERR_ARG, "mode must be SQZ_MODE_FAST or SQZ_MODE_FAITHFUL");
+  const int64_t nCs = ic1 - ic0;
+  if (S == 0 || nCs == 0 || nP == 0) return SQZ_OK;
+  if (S * nCs * nP > 0x7fffffffLL)
+    return fail(SQZ_ERR_SIZE, "more than 2^31-1 (sample, grid point) items in one shard");
+  CnModel m;
+  bool fast_ok;
+  int rc = build_cn_model(0, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          &fast_ok);
+  if (rc) return rc;
+  if (!workspace || ((uintptr_t)workspace & 255))
+    return fail(SQZ_ERR_ARG, "workspace must be non-null and 256-byte aligned");
+  Workspace w = carve(workspace, N_total, S, nP, nCs);
+  if (w.bytes > workspace_bytes) return fail(SQZ_ERR_SIZE, "workspace too small");
+
+  SQZ_CUDA(cudaMemcpyAsync(w.ploidy, h_ploidy, nP * sizeof(double), cudaMemcpyHostToDevice, st));
+  SQZ_CUDA(cudaMemcpyAsync(w.cell, h_cell + ic0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
+
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m);
+  BafGridArgs a;
+  a.S = S;
+  a.seg_off = d_seg_off;
+  a.Bf = d_Bf;
+  a.ratio = d_ratio;
+  a.sdBf = d_sdBf;
+  a.sdr = d_sdr;
+  a.wBf = d_wBf;
+  a.wr = d_wr;
+  a.rk = w.rk;
+  a.bk = w.bk;
+  a.nB = w.nB;
+  a.adr = d_adr;
+  a.ploidy = w.ploidy;
+  a.cell = w.cell;
+  a.nP = (int)nP;
+  a.nCs = (int)nCs;
+  a.nPT = g.nPT;
+  a.nChunk = g.nChunk;
+  a.rp = ratio_priority ? 1 : 0;
+  a.t5 = dt5_const();
+
+  const size_t sm_faith = (size_t)(m.nc + m.T) * sizeof(double);
+  const int faithful_ctas = 148 * 4;
+  if (mode == SQZ_MODE_FAITHFUL || !fast_ok) {
+    baf_grid_faithful_kernel<<<faithful_ctas, 256, sm_faith, st>>>(a, m, nullptr, nullptr, d_out);
+    SQZ_CUDA(cudaGetLastError());
+    return SQZ_OK;
+  }
+
+  SQZ_CUDA(cudaMemsetAsync(w.nB, 0, S * sizeof(int), st));
+  SQZ_CUDA(cudaMemsetAsync(w.fix_count, 0, sizeof(int), st));
+  {
+    const int64_t avg = (N_total + S - 1) / S;
+    int bx = (int)((avg + 255) / 256);
+    if (bx < 1) bx = 1;
+    if (bx > 1024) bx = 1024;
+    dim3 grid(bx, (unsigned)S);
+    if (S > 65535) return fail(SQZ_ERR_SIZE, "more than 65535 samples in one call");
+    baf_prep_kernel<<<grid, 256, 0, st>>>(a, w.rk, w.bk, w.nB);
+    SQZ_CUDA(cudaGetLastError());
+  }
+  {
+    const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;
+    if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
+    const size_t smb = (size_t)(m.nc * g.PT + m.T) * sizeof(double);
+    const bool rp = a.rp != 0;
+#define SQZ_LAUNCH_FAST(PTV)                                                              \
+  do {                                                                                    \
+    if (rp)                                                                               \
+      baf_grid_fast_kernel<PTV, true><<<(unsigned)ctas, g.threads, smb, st>>>(a, m, w.partM, w.partE); \
+    else                                                                                  \
+      baf_grid_fast_kernel<PTV, false><<<(unsigned)ctas, g.threads, smb, st>>>(a, m, w.partM, w.partE); \
+  } while (0)
+    if (g.PT == 8) SQZ_LAUNCH_FAST(8);
+    else if (g.PT == 16) SQZ_LAUNCH_FAST(16);
+    else SQZ_LAUNCH_FAST(32);
+#undef SQZ_LAUNCH_FAST
+    SQZ_CUDA(cudaGetLastError());
+  }
+  {
+    const int64_t items = S * nCs * nP;
+    baf_grid_finalize_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(
+        a, w.partM, w.partE, d_out, w.fix_list, w.fix_count);
+    SQZ_CUDA(cudaGetLastError());
+    baf_grid_faithful_kernel<<<faithful_ctas, 256, sm_faith, st>>>(a, m, w.fix_list,
+                                                                  w.fix_count, d_out);
+    SQZ_CUDA(cudaGetLastError());
+  }
+  return SQZ_OK;
+}
+
+int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_sdBf,
+                     const double* d_sdr, const double* d_wBf, const double* d_wr, int64_t N,
+                     double cellularity, double ploidy, double adr, int CNt_min, int CNt_max,
+                     int CNn, const double* prior_CN, const double* prior_value, int n_prior,
+                     int ratio_priority, cudaStream_t st, double* d_out) {
+  if (N < 0) return fail(SQZ_ERR_ARG, "negative N");
+  CnModel m;
+  int rc = build_cn_model(0, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          nullptr);
+  if (rc) return rc;
+  if (N == 0) return SQZ_OK;
+  int64_t blocks = (N + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  baf_point_kernel<<<(unsigned)blocks, 256, (size_t)(m.nc + m.T) * sizeof(double), st>>>(
+      N, d_Bf, d_ratio, d_sdBf, d_sdr, d_wBf, d_wr, cellularity, ploidy, adr, m,
+      ratio_priority ? 1 : 0, dt5_const(), d_out);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+}  // namespace sqz

@@ -1,0 +1,276 @@
+// sqz_mufreq.cu -- mufreq.bayes (R/bayes.R:126-173) and the mufreq.model.fit grid
+// (R/bayes.R:175-186), hand-written for sm_100a.
+//
+// Per position the reference evaluates, for every (CNt, Mt) row t,
+//   score.r[t] = dbinom(round(w.r * r/(1+r)), w.r, mr_t/(1+mr_t)) * prior_t   (R/bayes.R:25-29, :153)
+//   score.m[t] = dbinom(round(F * w.m), w.m, mufreq_t or 0.01)                 (R/bayes.R:1-6)
+//   post[t]    = score.r[t] * score.m[t],  exact zeros -> 1e-323               (R/bayes.R:155-156)
+// then takes CN* = CNt[which.max(score.r)] and the first maximum of log(post) among the
+// rows with CNt == CN* (R/bayes.R:157-164).
+//
+// The kernels keep R's nmath operation sequence (dbinom_raw, bd0, stirlerr) and only
+// remove repetition that cannot change a bit of the result:
+//   - score.r is the same number for all rows of one CNt, so it is evaluated once per
+//     copy number;
+//   - the three stirlerr terms and the lf term of dbinom_raw depend on (x, n) only, so
+//     they are evaluated once per position (and, for the grid, once per fit in a
+//     preparation pass) instead of once per row;
+//   - rows outside CN* never reach the output, so only the CN* rows get a score.m.
+#include "sqz_common.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+int build_cn_model(int kind, int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                   const double* prior_value, int n_prior, CnModel* m, bool* fast_ok);
+
+// model tables for one grid point: prob_r per copy number, model mufreq per row
+__device__ __forceinline__ void build_muf_model(const CnModel& m, double cell, double ploidy,
+                                                double adr, double* probr, double* mm) {
+  for (int c = threadIdx.x; c < m.nc; c += blockDim.x) {
+    double mr = theoretical_depth_ratio((double)(m.CNt_min + c), cell, ploidy,
+                                        (double)m.CNn, adr);
+    probr[c] = mr / (1 + mr);  // R/bayes.R:27
+  }
+  for (int t = threadIdx.x; t < m.T; t += blockDim.x) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    double v = theoretical_mufreq((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+                                  (double)m.CNn);
+    mm[t] = (v == 0) ? 0.01 : v;  // R/bayes.R:3 (seq.errors)
+  }
+}
+
+__device__ __forceinline__ void mufreq_eval(const CnModel& m, const double* probr,
+                                            const double* mm, const BinomHoist& hr,
+                                            const BinomHoist& hm, int& kc, int& kt,
+                                            double& lpp) {
+  kc = -1;
+  kt = 0;
+  double bests = 0.;
+  for (int c = 0; c < m.nc; ++c) {
+    const double sr = binom_finish(hr, probr[c]) * m.prior[c];
+    if (!isnan(sr) && (kc < 0 || sr > bests)) {  // which.max(score.r)
+      bests = sr;
+      kc = c;
+    }
+  }
+  if (kc < 0) {
+    lpp = __longlong_as_double(0x7FF8000000000000LL);
+    return;
+  }
+  int k = -1;
+  double best = 0.;
+  for (int t = m.toff[kc]; t < m.toff[kc + 1]; ++t) {
+    double post = bests * binom_finish(hm, mm[t]);
+    if (post == 0) post = __longlong_as_double(2LL);  // 1e-323, R/bayes.R:148, :156
+    const double lp = log(post);
+    if (!isnan(lp) && (k < 0 || lp > best)) {
+      best = lp;
+      k = t;
+    }
+  }
+  if (k < 0) {
+    kc = -1;
+    lpp = __longlong_as_double(0x7FF8000000000000LL);
+    return;
+  }
+  kt = k - m.toff[kc];
+  lpp = best;
+}
+
+__device__ __forceinline__ void hoist_position(double F, double ratio, double wm, double wr,
+                                               BinomHoist& hr, BinomHoist& hm) {
+  hr = binom_hoist(nearbyint(wr * (ratio / (1 + ratio))), wr);  // R/bayes.R:26
+  hm = binom_hoist(nearbyint(F * wm), wm);                      // R/bayes.R:4
+}
+
+__global__ void __launch_bounds__(256)
+mufreq_point_kernel(int64_t N, const double* F, const double* ratio, const double* wm,
+                    const double* wr, double cell, double ploidy, double adr, CnModel m,
+                    double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* probr = sm;
+  double* mm = sm + m.nc;
+  build_muf_model(m, cell, ploidy, adr, probr, mm);
+  __syncthreads();
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < N;
+       s += (int64_t)gridDim.x * blockDim.x) {
+    BinomHoist hr, hm;
+    hoist_position(F[s], ratio[s], wm[s], wr[s], hr, hm);
+    int kc, kt;
+    double lpp;
+    mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
+    out[s] = kc >= 0 ? (double)m.CNn : na_real();
+    out[N + s] = kc >= 0 ? (double)(m.CNt_min + kc) : na_real();
+    out[2 * N + s] = kc >= 0 ? (double)kt : na_real();
+    out[3 * N + s] = lpp;
+  }
+}
+
+__global__ void mufreq_prep_kernel(int64_t N, const double* F, const double* ratio,
+                                   const double* wm, const double* wr, BinomHoist* hr,
+                                   BinomHoist* hm) {
+  for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < N;
+       s += (int64_t)gridDim.x * blockDim.x)
+    hoist_position(F[s], ratio[s], wm[s], wr[s], hr[s], hm[s]);
+}
+
+// grid: persistent CTAs over this shard's grid points; threads stride over positions
+__global__ void __launch_bounds__(256)
+mufreq_grid_kernel(int64_t N, const BinomHoist* __restrict__ hr,
+                   const BinomHoist* __restrict__ hm, const double* __restrict__ ploidy,
+                   int nP, const double* __restrict__ cell, int nCs, double adr, CnModel m,
+                   double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* probr = sm;
+  double* mm = sm + m.nc;
+  __shared__ double red[3][8];
+  const int64_t items = (int64_t)nP * nCs;
+  for (int64_t g = blockIdx.x; g < items; g += gridDim.x) {
+    const int ic = (int)(g / nP), ip = (int)(g - (int64_t)ic * nP);
+    __syncthreads();
+    build_muf_model(m, cell[ic], ploidy[ip], adr, probr, mm);
+    __syncthreads();
+    DD acc = dd_zero();
+    for (int64_t s = threadIdx.x; s < N; s += blockDim.x) {
+      const BinomHoist a = hr[s], b = hm[s];
+      int kc, kt;
+      double lpp;
+      mufreq_eval(m, probr, mm, a, b, kc, kt, lpp);
+      dd_add(acc, lpp);
+    }
+    for (int off = 16; off; off >>= 1) {
+      DD o;
+      o.hi = __shfl_xor_sync(0xffffffffu, acc.hi, off);
+      o.lo = __shfl_xor_sync(0xffffffffu, acc.lo, off);
+      o.special = __shfl_xor_sync(0xffffffffu, acc.special, off);
+      dd_merge(acc, o);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+      red[0][warp] = acc.hi;
+      red[1][warp] = acc.lo;
+      red[2][warp] = acc.special;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      DD tot = dd_zero();
+      for (int w = 0; w < (int)((blockDim.x + 31) >> 5); ++w) {
+        DD o{red[0][w], red[1][w], red[2][w]};
+        dd_merge(tot, o);
+      }
+      out[g] = dd_value(tot);
+    }
+  }
+}
+
+__global__ void model_points_kernel(int kind, double cell, double ploidy, double adr,
+                                    CnModel m, double* out) {
+  const int T = m.T;
+  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    const double cn = (double)(m.CNt_min + c), second = (double)(t - m.toff[c]);
+    out[t] = cn;
+    out[T + t] = second;
+    out[2 * T + t] = theoretical_depth_ratio(cn, cell, ploidy, (double)m.CNn, adr);
+    out[3 * T + t] = kind == 0 ? theoretical_baf(cn, second, cell, (double)m.CNn)
+                               : theoretical_mufreq(cn, second, cell, (double)m.CNn);
+    out[4 * T + t] = m.prior[c];
+  }
+}
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nCs) {
+  const size_t n = (size_t)(N > 0 ? N : 1);
+  return 2 * align256(n * sizeof(BinomHoist)) + align256((size_t)(nP > 0 ? nP : 1) * 8) +
+         align256((size_t)(nCs > 0 ? nCs : 1) * 8);
+}
+
+int mufreq_point_launch(const double* d_F, const double* d_ratio, const double* d_wm,
+                        const double* d_wr, int64_t N, double cellularity, double ploidy,
+                        double adr, int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                        const double* prior_value, int n_prior, cudaStream_t st,
+                        double* d_out) {
+  if (N < 0) return fail(SQZ_ERR_ARG, "negative N");
+  CnModel m;
+  int rc = build_cn_model(1, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          nullptr);
+  if (rc) return rc;
+  if (N == 0) return SQZ_OK;
+  int64_t blocks = (N + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  mufreq_point_kernel<<<(unsigned)blocks, 256, (size_t)(m.nc + m.T) * sizeof(double), st>>>(
+      N, d_F, d_ratio, d_wm, d_wr, cellularity, ploidy, adr, m, d_out);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+int mufreq_grid_launch(const double* d_F, const double* d_ratio, const double* d_wm,
+                       const double* d_wr, int64_t N, const double* h_ploidy, int64_t nP,
+                       const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1, double adr,
+                       int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                       const double* prior_value, int n_prior, void* workspace,
+                       size_t workspace_bytes, cudaStream_t st, double* d_out) {
+  if (N < 0 || nP < 0 || nC < 0 || ic0 < 0 || ic1 > nC || ic0 > ic1)
+    return fail(SQZ_ERR_ARG, "negative size or bad cellularity shard");
+  const int64_t nCs = ic1 - ic0;
+  if (nCs == 0 || nP == 0) return SQZ_OK;
+  CnModel m;
+  int rc = build_cn_model(1, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          nullptr);
+  if (rc) return rc;
+  if (!workspace || ((uintptr_t)workspace & 255))
+    return fail(SQZ_ERR_ARG, "workspace must be non-null and 256-byte aligned");
+  if (mufreq_grid_workspace_bytes(N, nP, nCs) > workspace_bytes)
+    return fail(SQZ_ERR_SIZE, "workspace too small");
+  char* p = (char*)workspace;
+  const size_t n = (size_t)(N > 0 ? N : 1);
+  BinomHoist* hr = (BinomHoist*)p;
+  p += align256(n * sizeof(BinomHoist));
+  BinomHoist* hm = (BinomHoist*)p;
+  p += align256(n * sizeof(BinomHoist));
+  double* d_ploidy = (double*)p;
+  p += align256((size_t)nP * 8);
+  double* d_cell = (double*)p;
+  SQZ_CUDA(cudaMemcpyAsync(d_ploidy, h_ploidy, nP * sizeof(double), cudaMemcpyHostToDevice, st));
+  SQZ_CUDA(cudaMemcpyAsync(d_cell, h_cell + ic0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (N > 0) {
+    int64_t blocks = (N + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    mufreq_prep_kernel<<<(unsigned)blocks, 256, 0, st>>>(N, d_F, d_ratio, d_wm, d_wr, hr, hm);
+    SQZ_CUDA(cudaGetLastError());
+  }
+  int64_t ctas = nP * nCs;
+  if (ctas > 148 * 8) ctas = 148 * 8;
+  const int threads = N > 2048 ? 256 : 128;
+  mufreq_grid_kernel<<<(unsigned)ctas, threads, (size_t)(m.nc + m.T) * sizeof(double), st>>>(
+      N, hr, hm, d_ploidy, (int)nP, d_cell, (int)nCs, adr, m, d_out);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+int model_points_launch(int kind, double cellularity, double ploidy, double adr, int CNt_min,
+                        int CNt_max, int CNn, const double* prior_CN,
+                        const double* prior_value, int n_prior, int* T_out, double* h_out) {
+  if (kind != 0 && kind != 1) return fail(SQZ_ERR_ARG, "kind must be 0 (baf) or 1 (mufreq)");
+  CnModel m;
+  int rc = build_cn_model(kind, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          nullptr);
+  if (rc) return rc;
+  if (T_out) *T_out = m.T;
+  if (!h_out) return SQZ_OK;
+  double* d = nullptr;
+  SQZ_CUDA(cudaMalloc(&d, (size_t)m.T * 5 * sizeof(double)));
+  model_points_kernel<<<1, 128>>>(kind, cellularity, ploidy, adr, m, d);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess)
+    e = cudaMemcpy(h_out, d, (size_t)m.T * 5 * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(SQZ_ERR_CUDA, cudaGetErrorString(e));
+  return SQZ_OK;
+}
+
+}  // namespace sqz
