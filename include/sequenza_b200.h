@@ -169,6 +169,20 @@ int sqz_model_points(int kind, double cellularity, double ploidy, double avg_dep
  * --------------------------------------------------------------------------------- */
 int sqz_fp64_peak(int device, int repeats, double* tflops_out);
 
+/* Launch geometry the fast grid path would use, for reporting: out5 = ploidies per CTA
+ * tile, tiles per column, segment chunks, threads per CTA, number of (CNt, B) types.
+ * No counterpart in the reference. */
+int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, int CNt_min,
+                      int CNt_max, int CNn, int ratio_priority, int* out5);
+
+/* Per-kernel timing of fast-mode grid calls on the current device: after
+ * sqz_profile_enable(1), every sqz_baf_grid_dev / sqz_baf_grid call records CUDA events
+ * on its launch stream around (preparation | grid kernel | finalize + repair);
+ * sqz_profile_collect sums them in ms3[0..2] over *n_calls calls and resets.  The caller
+ * synchronises the stream before collecting.  No counterpart in the reference. */
+int sqz_profile_enable(int on);
+int sqz_profile_collect(double* ms3, int* n_calls);
+
 #ifdef __cplusplus
 }
 #endif

@@ -45,6 +45,9 @@ SIGNATURES = {
     "sqz_mufreq_grid_workspace_bytes": (_sz, [_i64, _i64, _i64]),
     "sqz_model_points": (_i, [_i, _d, _d, _d, _i, _i, _i, _p, _p, _i, _p, _p]),
     "sqz_fp64_peak": (_i, [_i, _i, _p]),
+    "sqz_baf_grid_plan": (_i, [_i64, _i64, _i64, _i64, _i, _i, _i, _i, _p]),
+    "sqz_profile_enable": (_i, [_i]),
+    "sqz_profile_collect": (_i, [_p, _p]),
 }
 
 _lib = None

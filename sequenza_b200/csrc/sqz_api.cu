@@ -34,6 +34,10 @@ int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_
                      double cellularity, double ploidy, double adr, int CNt_min, int CNt_max,
                      int CNn, const double* prior_CN, const double* prior_value, int n_prior,
                      int ratio_priority, cudaStream_t st, double* d_out);
+int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_min, int CNt_max,
+                  int CNn, int ratio_priority, int* out5);
+int profile_enable(int on);
+int profile_collect(double* ms3, int* n_calls);
 size_t mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nCs);
 int mufreq_point_launch(const double* d_F, const double* d_ratio, const double* d_wm,
                         const double* d_wr, int64_t N, double cellularity, double ploidy,
@@ -441,6 +445,15 @@ int sqz_model_points(int kind, double cellularity, double ploidy, double avg_dep
   return model_points_launch(kind, cellularity, ploidy, avg_depth_ratio, CNt_min, CNt_max,
                              CNn, prior_CN, prior_value, n_prior, T_out, out);
 }
+
+int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, int CNt_min,
+                      int CNt_max, int CNn, int ratio_priority, int* out5) {
+  if (!out5) return fail(SQZ_ERR_ARG, "out5 is null");
+  return baf_grid_plan(N_total, S, nP, nC_shard, CNt_min, CNt_max, CNn, ratio_priority, out5);
+}
+
+int sqz_profile_enable(int on) { return profile_enable(on); }
+int sqz_profile_collect(double* ms3, int* n_calls) { return profile_collect(ms3, n_calls); }
 
 int sqz_fp64_peak(int device, int repeats, double* tflops_out) {
   if (!tflops_out) return fail(SQZ_ERR_ARG, "tflops_out is null");

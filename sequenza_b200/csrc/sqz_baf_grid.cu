@@ -22,6 +22,8 @@
 // Anything non-finite (NaN model points at cellularity 1, zero sd, overflow) makes the
 // product Inf/NaN, which flags that grid point; flagged points are recomputed by the
 // faithful kernel below, which walks the nmath dt() sequence type by type.
+#include <vector>
+
 #include "sqz_common.cuh"
 #include "../../include/sequenza_b200.h"
 
@@ -469,18 +471,88 @@ int build_cn_model(int kind, int CNt_min, int CNt_max, int CNn, const double* pr
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// ---- optional per-kernel timing (sqz_profile_*): CUDA events recorded on the launch
+// stream around the three phases of a fast-mode grid call, read back after the caller
+// has synchronised.  Off by default; bench.py turns it on for the roofline numbers.
+struct ProfSet {
+  cudaEvent_t ev[4];
+};
+static bool g_prof_on = false;
+static int g_prof_dev = -1;
+static int g_prof_n = 0;
+static const int kProfMax = 4096;
+static std::vector<ProfSet>* g_prof = nullptr;
+
+int profile_enable(int on) {
+  g_prof_on = on != 0;
+  g_prof_n = 0;
+  return SQZ_OK;
+}
+
+static ProfSet* prof_next() {
+  if (!g_prof_on) return nullptr;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  if (!g_prof) g_prof = new std::vector<ProfSet>();
+  if (dev != g_prof_dev) {  // events belong to a device: start over on a device change
+    for (auto& p : *g_prof)
+      for (int k = 0; k < 4; ++k) cudaEventDestroy(p.ev[k]);
+    g_prof->clear();
+    g_prof_dev = dev;
+    g_prof_n = 0;
+  }
+  if (g_prof_n >= kProfMax) return nullptr;
+  if ((int)g_prof->size() <= g_prof_n) {
+    ProfSet p;
+    for (int k = 0; k < 4; ++k)
+      if (cudaEventCreate(&p.ev[k]) != cudaSuccess) return nullptr;
+    g_prof->push_back(p);
+  }
+  return &(*g_prof)[g_prof_n++];
+}
+
+// sums (ms) of prep / fast kernel / finalize+repair over the calls recorded since
+// profile_enable(1); the caller must have synchronised the stream(s).
+int profile_collect(double* ms3, int* n_calls) {
+  double acc[3] = {0, 0, 0};
+  int n = 0;
+  if (g_prof)
+    for (int i = 0; i < g_prof_n; ++i) {
+      float a = 0, b = 0, c = 0;
+      ProfSet& p = (*g_prof)[i];
+      if (cudaEventElapsedTime(&a, p.ev[0], p.ev[1]) != cudaSuccess ||
+          cudaEventElapsedTime(&b, p.ev[1], p.ev[2]) != cudaSuccess ||
+          cudaEventElapsedTime(&c, p.ev[2], p.ev[3]) != cudaSuccess) {
+        cudaGetLastError();
+        continue;
+      }
+      acc[0] += a;
+      acc[1] += b;
+      acc[2] += c;
+      ++n;
+    }
+  g_prof_n = 0;
+  if (ms3) {
+    ms3[0] = acc[0];
+    ms3[1] = acc[1];
+    ms3[2] = acc[2];
+  }
+  if (n_calls) *n_calls = n;
+  return SQZ_OK;
+}
+
 struct GridPlan {
   int PT, nPT, nChunk, threads;
 };
 
 static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
-                          const CnModel* m) {
+                          const CnModel* m, bool rp = false) {
   GridPlan g;
   const int cand[3] = {8, 16, 32};
   double bestc = 0;
   g.PT = 32;
   const int nc = m ? m->nc : 8, T = m ? m->T : 20;
-  for (int k = 0; k < 3; ++k) {
+  for (int k = 0; k < (rp ? 2 : 3); ++k) {  // PT = 32 spills registers with ratio.priority
     int pt = cand[k];
     double cost = (double)((nP + pt - 1) / pt) * (pt * (4.0 * nc + 1) + 2.0 * T + 2.0 * nc);
     if (k == 0 || cost < bestc) {
@@ -541,6 +613,22 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   return w;
 }
 
+// launch geometry of a fast-mode call, for reporting (bench.py roofline)
+int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_min, int CNt_max,
+                  int CNn, int ratio_priority, int* out5) {
+  CnModel m;
+  bool ok;
+  int rc = build_cn_model(0, CNt_min, CNt_max, CNn, nullptr, nullptr, 0, &m, &ok);
+  if (rc) return rc;
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0);
+  out5[0] = g.PT;
+  out5[1] = g.nPT;
+  out5[2] = g.nChunk;
+  out5[3] = g.threads;
+  out5[4] = m.T;
+  return SQZ_OK;
+}
+
 size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
   return carve(nullptr, N_total, S, nP, nCs).bytes;
 }
@@ -574,7 +662,7 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   SQZ_CUDA(cudaMemcpyAsync(w.ploidy, h_ploidy, nP * sizeof(double), cudaMemcpyHostToDevice, st));
   SQZ_CUDA(cudaMemcpyAsync(w.cell, h_cell + ic0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
 
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m);
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0);
   BafGridArgs a;
   a.S = S;
   a.seg_off = d_seg_off;
@@ -607,6 +695,8 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
 
   SQZ_CUDA(cudaMemsetAsync(w.nB, 0, S * sizeof(int), st));
   SQZ_CUDA(cudaMemsetAsync(w.fix_count, 0, sizeof(int), st));
+  ProfSet* prof = prof_next();
+  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[0], st));
   {
     const int64_t avg = (N_total + S - 1) / S;
     int bx = (int)((avg + 255) / 256);
@@ -617,6 +707,7 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     baf_prep_kernel<<<grid, 256, 0, st>>>(a, w.rk, w.bk, w.nB);
     SQZ_CUDA(cudaGetLastError());
   }
+  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[1], st));
   {
     const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;
     if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
@@ -635,6 +726,7 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
 #undef SQZ_LAUNCH_FAST
     SQZ_CUDA(cudaGetLastError());
   }
+  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[2], st));
   {
     const int64_t items = S * nCs * nP;
     baf_grid_finalize_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(
@@ -644,6 +736,7 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
                                                                   w.fix_count, d_out);
     SQZ_CUDA(cudaGetLastError());
   }
+  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[3], st));
   return SQZ_OK;
 }
 

@@ -40,8 +40,9 @@ def gather_columns(local: torch.Tensor, nC: int, nP: int, world: int, rank: int,
     if world == 1:
         recv = send.unsqueeze(0)
     else:
-        recv = torch.empty((world, S, width), dtype=local.dtype, device=local.device)
-        dist.all_gather_into_tensor(recv, send, group=group)
+        flat = torch.empty((world * S, width), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(flat, send, group=group)  # rank-major concatenation
+        recv = flat.view(world, S, width)
     full = torch.empty((S, nC * nP), dtype=local.dtype, device=local.device)
     for r in range(world):
         c0, c1 = shard_columns(nC, world, r)
