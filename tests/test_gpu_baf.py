@@ -28,8 +28,10 @@ def check_point(oracle, seg, cell, plo, **kw):
     got = S.baf_bayes(cellularity=cell, ploidy=plo, **baf_args(seg), **kw)
     ref, margin = oracle.baf_bayes(cellularity=cell, ploidy=plo, return_margin=True,
                                    **baf_args(seg), **kw)
-    # a state may differ only where the oracle's own top-2 gap is at rounding level
-    tie = margin < 1e-12
+    # a state may differ only where the oracle's own top-2 gap is at rounding level;
+    # exact ties (gap 0: e.g. Bf = NA makes every B of a CNt equal) must still match,
+    # because both sides take the first maximum
+    tie = (margin > 0) & (margin < 1e-12)
     for col in range(3):
         g, r = got[:, col], ref[:, col]
         same = (g == r) | (np.isnan(g) & np.isnan(r))
