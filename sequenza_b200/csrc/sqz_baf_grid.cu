@@ -22,6 +22,8 @@
 // Anything non-finite (NaN model points at cellularity 1, zero sd, overflow) makes the
 // product Inf/NaN, which flags that grid point; flagged points are recomputed by the
 // faithful kernel below, which walks the nmath dt() sequence type by type.
+#include <stdlib.h>
+
 #include <vector>
 
 #include "sqz_common.cuh"
@@ -79,7 +81,7 @@ __global__ void baf_prep_kernel(BafGridArgs a, double2* rk, double2* bk, int* nB
 
 // ---- fast grid kernel ---------------------------------------------------------------
 template <int PT, bool RP>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, ((PT <= 16 && !RP) ? 2 : 1))
 baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
                      long long* __restrict__ partE) {
   extern __shared__ double sm[];
@@ -166,13 +168,34 @@ baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
     }
     int t = 0;
     for (int c = 0; c < m.nc; ++c) {
-      // min over B of |xb| (first strict minimum; NaN never wins): R/bayes.R:70-72
+      // min over B of |xb| (NaN never wins): R/bayes.R:70-72.  Four independent running
+      // minima break the compare/select dependency chain; the signed value is kept and
+      // |.| is folded into the compare, so no fp64 slot is spent on fabs.
       const int tend = m.toff[c + 1];
-      double mabs = INF;
-      for (; t < tend; ++t) {
-        double ax = fabs(fma(mb[t], bk.x, bk.y));
-        if (ax < mabs) mabs = ax;
+      double m0 = INF, m1 = INF, m2 = INF, m3 = INF;
+      for (; t + 4 <= tend; t += 4) {
+        const double x0 = fma(mb[t], bk.x, bk.y), x1 = fma(mb[t + 1], bk.x, bk.y);
+        const double x2 = fma(mb[t + 2], bk.x, bk.y), x3 = fma(mb[t + 3], bk.x, bk.y);
+        if (fabs(x0) < fabs(m0)) m0 = x0;
+        if (fabs(x1) < fabs(m1)) m1 = x1;
+        if (fabs(x2) < fabs(m2)) m2 = x2;
+        if (fabs(x3) < fabs(m3)) m3 = x3;
       }
+      if (t + 2 <= tend) {
+        const double x0 = fma(mb[t], bk.x, bk.y), x1 = fma(mb[t + 1], bk.x, bk.y);
+        if (fabs(x0) < fabs(m0)) m0 = x0;
+        if (fabs(x1) < fabs(m1)) m1 = x1;
+        t += 2;
+      }
+      if (t < tend) {
+        const double x2 = fma(mb[t], bk.x, bk.y);
+        if (fabs(x2) < fabs(m2)) m2 = x2;
+        ++t;
+      }
+      if (fabs(m1) < fabs(m0)) m0 = m1;
+      if (fabs(m3) < fabs(m2)) m2 = m3;
+      if (fabs(m2) < fabs(m0)) m0 = m2;
+      const double mabs = m0;
       const double u = fma(mabs, mabs, 1.0);  // 1 + xb^2/5
       const double wc = m.w[c];
       const double wub = u * wc;
@@ -545,6 +568,18 @@ struct GridPlan {
   int PT, nPT, nChunk, threads;
 };
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+// Fraction of SM-time idle in the last wave when `ctas` CTAs run `per_sm` at a time.
+static double tail_waste(int64_t ctas, int per_sm) {
+  const int64_t slots = 148LL * per_sm;
+  const int64_t waves = (ctas + slots - 1) / slots;
+  return 1.0 - (double)ctas / (double)(waves * slots);
+}
+
 static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
                           const CnModel* m, bool rp = false) {
   GridPlan g;
@@ -560,16 +595,42 @@ static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
       g.PT = pt;
     }
   }
+  const int pt_env = env_int("SQZ_PT", 0);  // tuning overrides (experiments only)
+  if (pt_env == 8 || pt_env == 16 || (pt_env == 32 && !rp)) g.PT = pt_env;
   g.nPT = (int)((nP + g.PT - 1) / g.PT);
   const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
-  g.threads = avg > 1024 ? 256 : (avg > 64 ? 128 : 64);
+  // 128-thread CTAs: two resident per SM even at 255 registers, finer tail granularity
+  g.threads = avg > 64 ? 128 : 64;
+  const int th_env = env_int("SQZ_THREADS", 0);
+  if (th_env == 64 || th_env == 128 || th_env == 256) g.threads = th_env;
+  // resident CTAs per SM from the register budget of each instantiation
+  const int regs = (g.PT == 32 || rp) ? 256 : 128;
+  int per_sm = 65536 / (regs * g.threads);
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  // Split each sample's segments into chunks until the grid fills the machine for a
+  // few waves, then pick the chunk count with the smallest idle tail in that range.
   const int64_t base = S * nCs * g.nPT;
-  int64_t want = base > 0 ? (148 * 2 * 3 + base - 1) / base : 1;  // ~3 waves of 2 CTAs/SM
-  int64_t cap = avg / ((int64_t)g.threads * 8);
-  if (want > cap) want = cap;
-  if (want < 1) want = 1;
-  if (want > 64) want = 64;
-  g.nChunk = (int)want;
+  int64_t cap = avg / ((int64_t)g.threads * 8);  // keep >= 8 segments per thread
+  if (cap < 1) cap = 1;
+  if (cap > 64) cap = 64;
+  int64_t lo = base > 0 ? (148LL * per_sm * 3 + base - 1) / base : 1;
+  if (lo > cap) lo = cap;
+  if (lo < 1) lo = 1;
+  int64_t hi = lo * 2 + 2;
+  if (hi > cap) hi = cap;
+  int64_t best = lo;
+  double bw = 2.0;
+  for (int64_t k = lo; k <= hi; ++k) {
+    double wst = tail_waste(base * k, per_sm) + 0.002 * (double)(k - lo);  // mild bias to fewer
+    if (wst < bw) {
+      bw = wst;
+      best = k;
+    }
+  }
+  g.nChunk = (int)best;
+  const int ch_env = env_int("SQZ_CHUNKS", 0);
+  if (ch_env >= 1 && ch_env <= 64) g.nChunk = ch_env;
   return g;
 }
 
@@ -595,9 +656,10 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   };
   const size_t n = (size_t)(N_total > 0 ? N_total : 1);
   const size_t items = (size_t)(S * nCs * nP > 0 ? S * nCs * nP : 1);
-  // nChunk depends on nPT (PT); bound it for any PT the planner may choose
-  int64_t base_min = S * nCs * ((nP + 31) / 32);
-  int64_t want = base_min > 0 ? (148 * 2 * 3 + base_min - 1) / base_min : 1;
+  // partials are sized for the largest chunk count the planner may pick (64), bounded
+  // by what the segment count allows (>= 8 segments per thread, >= 64 threads)
+  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+  int64_t want = avg / (64 * 8);
   if (want > 64) want = 64;
   if (want < 1) want = 1;
   w.rk = (double2*)take(n * sizeof(double2));
