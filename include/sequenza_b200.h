@@ -95,6 +95,49 @@ int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
                      double* d_lpp_sum_out);
 
 /* ---------------------------------------------------------------------------------
+ * Grid fit for callers that cannot allocate device memory.  This entry point has no
+ * counterpart in the reference.
+ *
+ * Who needs it: code that runs where cudaMalloc is off limits -- a host thread inside a
+ * real-time or latency-bounded loop (cudaMalloc/cudaFree take a driver lock and may
+ * synchronise the whole device), a plugin whose embedding application owns the memory
+ * budget and forbids further allocations after start-up, or a process that has already
+ * handed all free device memory to another pool and would simply get an out-of-memory
+ * error.  Such callers still own their input and output buffers, but have nowhere to
+ * get the workspace that sqz_baf_grid_dev asks for.
+ *
+ * What it does: exactly what sqz_baf_grid_dev does (same arguments minus the workspace,
+ * same kernels, same results), with the scratch taken from a fixed 16 MiB array that is
+ * part of the library image on every GPU that loads it.  The call performs no
+ * cudaMalloc, cudaFree or other allocating call.
+ *
+ * Limits and rules:
+ *   - the problem must fit: sqz_baf_grid_workspace_bytes(N_total, S, nP, ic1 - ic0) must
+ *     be <= 16 MiB (16,777,216 bytes); larger problems are refused with SQZ_ERR_SIZE and
+ *     a message naming both numbers.  BASELINE config 2 (3e4 segments, 91 x 61 grid)
+ *     needs about 5.9 MiB;
+ *   - the first call on each device looks up the device address of the built-in scratch
+ *     (one cudaGetSymbolAddress); make that first call before starting any stream
+ *     capture on that device;
+ *   - all calls on a device share the one scratch array, and it keeps whatever the
+ *     previous call left in it (each call re-initialises the parts it needs zeroed).
+ *     Two calls whose GPU work overlaps in time -- different streams, or different host
+ *     threads -- race on it and corrupt each other's results.  Issue the calls on one
+ *     stream, or order them with events;
+ *   - per-kernel timing (sqz_profile_enable) is ignored by this entry point.
+ * --------------------------------------------------------------------------------- */
+int sqz_baf_grid_dev_noalloc(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
+                             const double* d_Bf, const double* d_depth_ratio,
+                             const double* d_sd_Bf, const double* d_sd_ratio,
+                             const double* d_weight_Bf, const double* d_weight_ratio,
+                             const double* ploidy, int64_t nP, const double* cellularity,
+                             int64_t nC, int64_t ic0, int64_t ic1,
+                             const double* d_avg_depth_ratio, int CNt_min, int CNt_max,
+                             int CNn, const double* prior_CN, const double* prior_value,
+                             int n_prior, int ratio_priority, int mode, void* stream,
+                             double* d_lpp_sum_out);
+
+/* ---------------------------------------------------------------------------------
  * B2  baf.bayes at one (cellularity, ploidy) -- replaces R/bayes.R:46-98.
  * out is N x 4 column-major: CNt, A, B, LPP (R/bayes.R:99).  Callers: R/results.R:128,
  * :139, R/graphics.R:419.  Rows whose posterior is NaN for every type (the reference

@@ -32,6 +32,8 @@ SIGNATURES = {
     "sqz_baf_grid_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
     "sqz_baf_grid_dev": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64, _i64,
                               _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _sz, _p, _p]),
+    "sqz_baf_grid_dev_noalloc": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64,
+                                      _i64, _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _p]),
     "sqz_baf_point": (_i, [_p] * 6 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _i, _p]),
     "sqz_baf_point_dev": (_i, [_p] * 6 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _i, _p,
                                _p]),

@@ -24,6 +24,7 @@
 // faithful kernel below, which walks the nmath dt() sequence type by type.
 #include <stdlib.h>
 
+#include <mutex>
 #include <vector>
 
 #include "sqz_common.cuh"
@@ -822,4 +823,71 @@ int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_
   return SQZ_OK;
 }
 
+// ---- grid fit for callers that must not allocate ------------------------------------
+// Same kernels as sqz_baf_grid_dev; the only difference is where the scratch lives.
+// Instead of a caller-provided workspace it is this fixed array inside the library
+// image, so the call path contains no cudaMalloc/cudaFree and no allocating routine.
+// Every GPU that loads the library carries these bytes until the process exits.
+constexpr size_t kNoAllocScratchBytes = 16u << 20;  // 16 MiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not an address a
+// kernel can use; the device address is looked up once per device and kept here.
+constexpr int kMaxDevices = 64;
+static void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  SQZ_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(SQZ_ERR_SIZE, "device ordinal beyond the 64 this entry point tracks");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    SQZ_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // with `dev` current
+    if (!p) return fail(SQZ_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return SQZ_OK;
+}
+
 }  // namespace sqz
+
+extern "C" int sqz_baf_grid_dev_noalloc(
+    int64_t S, const int64_t* d_seg_offsets, int64_t N_total, const double* d_Bf,
+    const double* d_depth_ratio, const double* d_sd_Bf, const double* d_sd_ratio,
+    const double* d_weight_Bf, const double* d_weight_ratio, const double* ploidy, int64_t nP,
+    const double* cellularity, int64_t nC, int64_t ic0, int64_t ic1,
+    const double* d_avg_depth_ratio, int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+    const double* prior_value, int n_prior, int ratio_priority, int mode, void* stream,
+    double* d_lpp_sum_out) {
+  using namespace sqz;
+  if (S < 0 || N_total < 0 || nP < 0 || nC < 0 || ic0 < 0 || ic1 > nC || ic0 > ic1)
+    return fail(SQZ_ERR_ARG, "negative size or bad cellularity shard");
+  const size_t need = baf_grid_workspace_bytes(N_total, S, nP, ic1 - ic0);
+  if (need > kNoAllocScratchBytes) {
+    char msg[256];
+    snprintf(msg, sizeof msg,
+             "sqz_baf_grid_dev_noalloc: this problem needs %zu bytes of scratch but the "
+             "built-in scratch is %zu bytes (16 MiB); use sqz_baf_grid_dev with a "
+             "caller-owned workspace instead",
+             need, kNoAllocScratchBytes);
+    return fail(SQZ_ERR_SIZE, msg);
+  }
+  void* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  // the optional per-kernel timing creates CUDA events on first use; keep it out of a
+  // path that promises not to allocate
+  const bool prof_was_on = g_prof_on;
+  g_prof_on = false;
+  rc = baf_grid_launch(S, d_seg_offsets, N_total, d_Bf, d_depth_ratio, d_sd_Bf, d_sd_ratio,
+                       d_weight_Bf, d_weight_ratio, ploidy, nP, cellularity, nC, ic0, ic1,
+                       d_avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
+                       n_prior, ratio_priority, mode, scratch, kNoAllocScratchBytes,
+                       (cudaStream_t)stream, d_lpp_sum_out);
+  g_prof_on = prof_was_on;
+  return rc;
+}

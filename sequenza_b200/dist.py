@@ -105,6 +105,30 @@ class BafGridDevice:
         return out
 
 
+def run_noalloc(dev: "BafGridDevice", ploidy, cellularity, ic0=0, ic1=None, CNt_min=0,
+                CNt_max=7, CNn=2, priors_table=None, ratio_priority=False,
+                mode=_lib.SQZ_MODE_FAST, out=None):
+    """BafGridDevice.run through sqz_baf_grid_dev_noalloc: the library's built-in 16 MiB
+    scratch replaces the torch-allocated workspace, for embedders that must not trigger
+    device allocations once they are running.  `out` should be preallocated by such a
+    caller (it is allocated here only when omitted).  Calls on one device share the
+    scratch: keep them on one stream."""
+    pl, ce = _lib.vec(ploidy), _lib.vec(cellularity)
+    ic1 = ce.size if ic1 is None else ic1
+    pc, pv = _priors(priors_table, CNt_min, CNt_max)
+    if out is None:
+        out = torch.empty((dev.S, (ic1 - ic0) * pl.size), dtype=torch.float64,
+                          device=dev.device)
+    stream = torch.cuda.current_stream(dev.device).cuda_stream
+    with torch.cuda.device(dev.device):
+        _lib.check(_lib.lib().sqz_baf_grid_dev_noalloc(
+            dev.S, dev.d_off.data_ptr(), dev.N, *[t.data_ptr() for t in dev.d_inputs],
+            _lib.ptr(pl), pl.size, _lib.ptr(ce), ce.size, ic0, ic1, dev.d_adr.data_ptr(),
+            int(CNt_min), int(CNt_max), int(CNn), _lib.ptr(pc), _lib.ptr(pv), pc.size,
+            int(bool(ratio_priority)), int(mode), stream, out.data_ptr()))
+    return out
+
+
 def baf_model_fit_distributed(cellularity, ploidy, group=None, **kwargs):
     """baf.model.fit (R/bayes.R:103-124) across the ranks of an initialised
     torch.distributed job: every rank passes the same arguments, evaluates its block of
