@@ -81,8 +81,16 @@ int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
  * are DEVICE pointers; ploidy / cellularity / priors are HOST pointers (they
  * parameterise the launch).  Evaluates cellularity columns ic0 <= ic < ic1 only and
  * writes S x ((ic1-ic0)*nP) doubles to d_lpp_sum_out (device).  workspace must hold
- * sqz_baf_grid_workspace_bytes(...) bytes, 256-byte aligned. */
+ * at least sqz_baf_grid_workspace_bytes(...) bytes, 256-byte aligned. */
 size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard);
+/* The minimum above selects the fused kernel.  With more room the library runs the faster
+ * split form (a per-column pre-pass whose output, 16 * n_copy_numbers * N_total bytes per
+ * cellularity column, is streamed back by the grid kernel; columns are processed in
+ * batches that fit).  This returns minimum + as many columns as fit under cap_bytes
+ * (0 = no cap; at least one column).  n_copy_numbers = CNt_max - CNt_min + 1. */
+size_t sqz_baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP,
+                                              int64_t nC_shard, int n_copy_numbers,
+                                              size_t cap_bytes);
 int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
                      const double* d_Bf, const double* d_depth_ratio,
                      const double* d_sd_Bf, const double* d_sd_ratio,

@@ -30,6 +30,7 @@ SIGNATURES = {
     "sqz_baf_grid_batch": (_i, [_i64, _p] + [_p] * 6 + [_p, _i64, _p, _i64, _p, _i, _i, _i,
                                 _p, _p, _i, _i, _i, _i, _p]),
     "sqz_baf_grid_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
+    "sqz_baf_grid_workspace_preferred_bytes": (_sz, [_i64, _i64, _i64, _i64, _i, _sz]),
     "sqz_baf_grid_dev": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64, _i64,
                               _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _sz, _p, _p]),
     "sqz_baf_grid_dev_noalloc": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64,

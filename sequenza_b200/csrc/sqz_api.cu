@@ -21,6 +21,8 @@ int fail(int code, const std::string& msg) {
 
 // launchers (sqz_baf_grid.cu, sqz_mufreq.cu)
 size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs);
+size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
+                                          int n_copy_numbers, size_t cap_bytes);
 int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
                     const double* d_ratio, const double* d_sdBf, const double* d_sdr,
                     const double* d_wBf, const double* d_wr, const double* h_ploidy,
@@ -146,7 +148,9 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
     const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
     const size_t in_need = 6 * vbytes + a256((size_t)(S + 1) * 8) + a256((size_t)S * 8);
     if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
-    const size_t ws_need = baf_grid_workspace_bytes(N, S, nP, nCs);
+    const size_t ws_need = baf_grid_workspace_preferred_bytes(N, S, nP, nCs,
+                                                              CNt_max - CNt_min + 1,
+                                                              (size_t)2 << 30);
     if ((rc = grow(&c->ws, &c->ws_cap, ws_need))) return rc;
     if ((rc = grow(&c->out, &c->out_cap, (size_t)(S * nCs * nP) * 8))) return rc;
     char* p = (char*)c->in;
@@ -296,6 +300,12 @@ int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
 
 size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard) {
   return baf_grid_workspace_bytes(N_total, S, nP, nC_shard);
+}
+
+size_t sqz_baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP,
+                                              int64_t nC_shard, int n_copy_numbers,
+                                              size_t cap_bytes) {
+  return baf_grid_workspace_preferred_bytes(N_total, S, nP, nC_shard, n_copy_numbers, cap_bytes);
 }
 
 int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,

@@ -28,24 +28,10 @@
 #include <vector>
 
 #include "sqz_common.cuh"
+#include "sqz_baf_grid.cuh"
 #include "../../include/sequenza_b200.h"
 
 namespace sqz {
-
-struct BafGridArgs {
-  int64_t S;
-  const int64_t* seg_off;  // [S+1]
-  const double *Bf, *ratio, *sdBf, *sdr, *wBf, *wr;  // raw per-segment vectors
-  const double2* rk;  // fast path: (kr, er)   xr/sqrt5 = fma(log mr, kr, er)
-  const double2* bk;  // fast path: (kb, eb)   xb/sqrt5 = fma(mb, kb, eb)
-  const int* nB;      // [S] segments that carry a BAF term
-  const double* adr;  // [S] avg.depth.ratio
-  const double* ploidy;  // [nP]
-  const double* cell;    // [nCs] this shard's cellularities
-  int nP, nCs, nPT, nChunk;
-  int rp;
-  double t5;
-};
 
 // ---- per-segment preparation for the fast path ------------------------------------
 __global__ void baf_prep_kernel(BafGridArgs a, double2* rk, double2* bk, int* nB) {
@@ -696,6 +682,18 @@ size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t 
   return carve(nullptr, N_total, S, nP, nCs).bytes;
 }
 
+// minimum + room for the pre-pass output of as many columns as fit under `cap_bytes`
+size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
+                                          int n_copy_numbers, size_t cap_bytes) {
+  const size_t base = carve(nullptr, N_total, S, nP, nCs).bytes;
+  if (n_copy_numbers < 1 || n_copy_numbers > kMaxCN || nCs < 1) return base;
+  const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
+  size_t cols = (size_t)nCs;
+  if (cap_bytes > 0 && cols * per_col > cap_bytes) cols = cap_bytes / per_col;
+  if (cols < 1) cols = 1;
+  return base + align256(cols * per_col);
+}
+
 int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
                     const double* d_ratio, const double* d_sdBf, const double* d_sdr,
                     const double* d_wBf, const double* d_wr, const double* h_ploidy,
@@ -771,7 +769,17 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     SQZ_CUDA(cudaGetLastError());
   }
   if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[1], st));
-  {
+  // Split path when the workspace has room for at least one column of pre-pass output
+  // (sqz_baf_grid_workspace_preferred_bytes); fused kernel otherwise.
+  char* cw_buf = (char*)workspace + w.bytes;
+  const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
+  const bool use_split = env_int("SQZ_SPLIT", 1) != 0 && N_total > 0 &&
+                         baf_split_supported(m.nc, g.PT, g.threads) &&
+                         cw_bytes >= baf_split_column_bytes(m.nc, N_total);
+  if (use_split) {
+    rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st);
+    if (rc) return rc;
+  } else {
     const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;
     if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
     const size_t smb = (size_t)(m.nc * g.PT + m.T) * sizeof(double);

@@ -1,0 +1,315 @@
+// sqz_baf_split.cu -- split form of the baf.model.fit fast path (see sqz_baf_grid.cu for
+// the mathematics and for the fused fallback).
+//
+// The factor  wub[c] = prior_c^(-1/3) * min_B (1 + xb^2/5)  of a segment depends on the
+// cellularity and the copy number, not on the ploidy.  A grid column (one cellularity)
+// has nP/PT ploidy tiles, so the fused kernel recomputes it nP/PT times.  Here:
+//
+//   baf_colterm_kernel   one thread per (cellularity, segment): the min over B for every
+//                        copy number, stored as (wub, sqrt(wub)) in a column-major scratch
+//                        [column][CNt][segment] (coalesced over segments);
+//   baf_grid_split_kernel one CTA per (sample, cellularity, ploidy tile, segment chunk):
+//                        every thread streams its segments' scratch rows into its own
+//                        shared-memory column with cp.async, double-buffered one segment
+//                        ahead, and evaluates
+//                            q = (xr' * sqrt(wub))^2 + wub            (2 DFMA)
+//                            qmin = min(qmin, q)                      (DSETP + 2 FSEL)
+//                        for PT ploidies per copy number.  Running products stay in
+//                        registers, their binary exponents in shared memory.
+//
+// On B200 every warp-wide math instruction (fp64 or the selects of the running minimum)
+// holds the SMSP math dispatch for ~2.2 cycles and they do not overlap
+// (tools/microbench*.cu), so the kernel is built to minimise math instructions per
+// (copy number, ploidy): 5 here against 6.8 in the fused kernel.
+#include "sqz_baf_grid.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+// ---- pre-pass: BAF factor per (column, copy number, segment) ---------------------------
+__global__ void __launch_bounds__(256)
+baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
+                   double2* __restrict__ cw) {
+  extern __shared__ __align__(16) double sm[];
+  double* mb = sm;  // [T] model BAF of this column (R/model.R:9-14)
+  const double cell = a.cell[ic0 + blockIdx.y];
+  for (int t = threadIdx.x; t < m.T; t += blockDim.x) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    mb[t] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+                            (double)m.CNn);
+  }
+  __syncthreads();
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= N_total) return;
+  const double2 bk = a.bk[s];
+  double2* out = cw + (int64_t)blockIdx.y * m.nc * N_total + s;
+  int t = 0;
+  for (int c = 0; c < m.nc; ++c) {
+    // min over B of |xb|: NaN never wins (R/bayes.R:70-72, which.max skips NaN); four
+    // independent running minima, |.| folded into the compare
+    const int tend = m.toff[c + 1];
+    double m0 = INF, m1 = INF, m2 = INF, m3 = INF;
+    for (; t + 4 <= tend; t += 4) {
+      const double x0 = fma(mb[t], bk.x, bk.y), x1 = fma(mb[t + 1], bk.x, bk.y);
+      const double x2 = fma(mb[t + 2], bk.x, bk.y), x3 = fma(mb[t + 3], bk.x, bk.y);
+      if (fabs(x0) < fabs(m0)) m0 = x0;
+      if (fabs(x1) < fabs(m1)) m1 = x1;
+      if (fabs(x2) < fabs(m2)) m2 = x2;
+      if (fabs(x3) < fabs(m3)) m3 = x3;
+    }
+    for (; t < tend; ++t) {
+      const double x0 = fma(mb[t], bk.x, bk.y);
+      if (fabs(x0) < fabs(m0)) m0 = x0;
+    }
+    if (fabs(m1) < fabs(m0)) m0 = m1;
+    if (fabs(m3) < fabs(m2)) m2 = m3;
+    if (fabs(m2) < fabs(m0)) m0 = m2;
+    const double u = fma(m0, m0, 1.0);  // 1 + xb^2/5
+    if (a.rp) {
+      out[(int64_t)c * N_total] = make_double2(u, 0.0);
+    } else {
+      const double wub = u * m.w[c];
+      out[(int64_t)c * N_total] = make_double2(wub, sqrt(wub));
+    }
+  }
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ---- grid kernel ------------------------------------------------------------------------
+template <int PT, bool RP>
+__global__ void __launch_bounds__(128, 2)
+baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
+                      int nCb, int64_t N_total, double* __restrict__ partM,
+                      long long* __restrict__ partE) {
+  extern __shared__ __align__(16) double sm[];
+  const int nthr = blockDim.x, tid = threadIdx.x;
+  double* lmr = sm;                                                // [nc][PT]
+  double2* stage = reinterpret_cast<double2*>(sm + m.nc * PT);    // [2][nc][nthr]
+  int* Ec = reinterpret_cast<int*>(stage + 2 * m.nc * nthr);      // [PT][nthr]
+  __shared__ double redM[4][PT];
+  __shared__ long long redE[4][PT];
+  __shared__ unsigned redBad[4];
+
+  int64_t b = blockIdx.x;
+  const int pt = (int)(b % a.nPT);
+  b /= a.nPT;
+  const int icl = (int)(b % nCb);
+  b /= nCb;
+  const int chunk = (int)(b % a.nChunk);
+  const int64_t smp = b / a.nChunk;
+  const int ic = ic0 + icl;
+  const int p0 = pt * PT;
+
+  // log model depth ratio of this (cellularity, ploidy tile): R/model.R:1-7, :49-56
+  const double cell = a.cell[ic];
+  const double adr = a.adr[smp];
+  for (int i = tid; i < m.nc * PT; i += nthr) {
+    const int c = i / PT, j = i - c * PT;
+    const int ip = min(p0 + j, a.nP - 1);  // ragged last tile repeats the last ploidy
+    lmr[i] = log(theoretical_depth_ratio((double)(m.CNt_min + c), cell, a.ploidy[ip],
+                                         (double)m.CNn, adr));
+  }
+#pragma unroll
+  for (int j = 0; j < PT; ++j) Ec[j * nthr + tid] = 0;
+  __syncthreads();
+
+  const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
+  const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
+  const int64_t cb = s0 + (int64_t)chunk * per;
+  const int64_t ce = min(cb + per, s1);
+  const double2* cwc = cw + (int64_t)icl * m.nc * N_total;  // this column's scratch rows
+
+  double P[PT];
+#pragma unroll
+  for (int j = 0; j < PT; ++j) P[j] = 1.0;
+  unsigned bad = 0;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+
+  // Each thread copies only its own 16-byte entries and reads only those back, so
+  // cp.async.wait_group is all the synchronisation the staging needs.
+  auto issue = [&](int buf, int64_t seg) {
+    double2* dst = stage + (buf * m.nc) * nthr + tid;
+    const double2* src = cwc + seg;
+    for (int c = 0; c < m.nc; ++c) cp_async16(dst + c * nthr, src + (int64_t)c * N_total);
+    cp_async_commit();
+  };
+
+  int64_t s = cb + tid;
+  double2 rk_n = make_double2(0., 0.);
+  if (s < ce) {
+    rk_n = a.rk[s];
+    issue(0, s);
+  }
+  int it = 0, buf = 0;
+  while (s < ce) {
+    const double2 rk = rk_n;
+    const int64_t sn = s + nthr;
+    if (sn < ce) {  // next segment of this thread: ratio terms to registers, BAF rows to smem
+      rk_n = a.rk[sn];
+      issue(buf ^ 1, sn);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    const double2* col = stage + (buf * m.nc) * nthr + tid;
+
+    double qmin[PT];
+    double sel[RP ? PT : 1];
+#pragma unroll
+    for (int j = 0; j < PT; ++j) qmin[j] = INF;
+    if (RP) {
+#pragma unroll
+      for (int j = 0; j < (RP ? PT : 1); ++j) sel[j] = 1.0;
+    }
+#pragma unroll 2
+    for (int c = 0; c < m.nc; ++c) {
+      const double2 cwv = col[c * nthr];
+      const double* l = lmr + c * PT;
+      if (!RP) {
+        const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
+#pragma unroll
+        for (int j = 0; j < PT; ++j) {
+          const double x = fma(l[j], krw, erw);
+          const double q = fma(x, x, cwv.x);
+          if (q < qmin[j]) qmin[j] = q;  // strict <: first minimum, NaN never wins
+        }
+      } else {
+        // ratio.priority: CNt chosen on the ratio score alone (R/bayes.R:81-88)
+        const double wc = m.w[c];
+#pragma unroll
+        for (int j = 0; j < PT; ++j) {
+          const double x = fma(l[j], rk.x, rk.y);
+          const double ar = fma(x, x, 1.0) * wc;
+          if (ar < qmin[j]) {
+            qmin[j] = ar;
+            sel[RP ? j : 0] = cwv.x;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PT; ++j) P[j] *= RP ? qmin[j] * sel[RP ? j : 0] : qmin[j];
+    if ((++it & 3) == 0) {
+      // every 4th segment: binary exponent -> integer column (q >= 1; four factors cannot
+      // overflow unless one is already beyond 2^255, which is caught as "bad")
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+        if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+        Ec[j * nthr + tid] += (hi >> 20) - 1023;
+        P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+      }
+    }
+    s = sn;
+    buf ^= 1;
+  }
+
+  // CTA reduction: sum of log(mantissa) (each in [0, log 2)), exact integer exponents
+  const int lane = tid & 31, warp = tid >> 5, nwarp = (nthr + 31) >> 5;
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+    if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+    double v = log(__hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo));
+    long long e = (long long)Ec[j * nthr + tid] + ((hi >> 20) - 1023);
+    for (int off = 16; off; off >>= 1) {
+      v += __shfl_xor_sync(0xffffffffu, v, off);
+      e += __shfl_xor_sync(0xffffffffu, e, off);
+    }
+    if (lane == 0) {
+      redM[warp][j] = v;
+      redE[warp][j] = e;
+    }
+  }
+  for (int off = 16; off; off >>= 1) bad |= __shfl_xor_sync(0xffffffffu, bad, off);
+  if (lane == 0) redBad[warp] = bad;
+  __syncthreads();
+  if (tid < PT && p0 + tid < a.nP) {
+    double v = 0.;
+    long long e = 0;
+    unsigned bd = 0;
+    for (int w = 0; w < nwarp; ++w) {
+      v += redM[w][tid];
+      e += redE[w][tid];
+      bd |= redBad[w];
+    }
+    if ((bd >> tid) & 1u) v = __longlong_as_double(0x7FF8000000000000LL);
+    const int64_t Gs = (int64_t)a.nCs * a.nP;
+    const int64_t o = ((int64_t)chunk * a.S + smp) * Gs + (int64_t)ic * a.nP + p0 + tid;
+    partM[o] = v;
+    partE[o] = e;
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+size_t baf_split_column_bytes(int nc, int64_t N_total) {
+  return (size_t)nc * (size_t)(N_total > 0 ? N_total : 1) * sizeof(double2);
+}
+
+static size_t split_smem_bytes(int nc, int PT, int threads) {
+  return (size_t)nc * PT * sizeof(double) + (size_t)2 * nc * threads * sizeof(double2) +
+         (size_t)PT * threads * sizeof(int);
+}
+
+bool baf_split_supported(int nc, int PT, int threads) {
+  return threads <= 128 && split_smem_bytes(nc, PT, threads) <= 200 * 1024;
+}
+
+template <int PT, bool RP>
+static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
+                        const double2* cw, int ic0, int nCb, double* partM, long long* partE,
+                        cudaStream_t st) {
+  const size_t smb = split_smem_bytes(m.nc, PT, threads);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_split_kernel<PT, RP>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
+  if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
+  baf_grid_split_kernel<PT, RP><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb,
+                                                                      N_total, partM, partE);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+// Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
+int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
+                  void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
+                  cudaStream_t st) {
+  const size_t per_col = baf_split_column_bytes(m.nc, N_total);
+  int64_t nCb_max = (int64_t)(cw_bytes / per_col);
+  if (nCb_max < 1) return fail(SQZ_ERR_SIZE, "split path needs room for one column");
+  if (nCb_max > a.nCs) nCb_max = a.nCs;
+  double2* cw = (double2*)cw_buf;
+  const bool rp = a.rp != 0;
+  for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += nCb_max) {
+    const int nCb = (int)((a.nCs - ic0 < nCb_max) ? (a.nCs - ic0) : nCb_max);
+    dim3 grid((unsigned)((N_total + 255) / 256), (unsigned)nCb);
+    baf_colterm_kernel<<<grid, 256, (size_t)m.T * sizeof(double), st>>>(a, m, (int)ic0, N_total,
+                                                                        cw);
+    SQZ_CUDA(cudaGetLastError());
+    int rc;
+#define SQZ_SPLIT(PTV)                                                                     \
+  rc = rp ? launch_split<PTV, true>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st) \
+          : launch_split<PTV, false>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st)
+    if (PT == 8) SQZ_SPLIT(8);
+    else if (PT == 16) SQZ_SPLIT(16);
+    else SQZ_SPLIT(32);
+#undef SQZ_SPLIT
+    if (rc) return rc;
+  }
+  return SQZ_OK;
+}
+
+}  // namespace sqz

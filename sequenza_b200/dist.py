@@ -71,6 +71,7 @@ class BafGridDevice:
         self.h_off_t = torch.from_numpy(self.h_offsets).pin_memory()
         self.upload()
         self._ws = None
+        self.ws_cap = 2 << 30  # bytes of pre-pass scratch the grid fit may use per call
 
     def upload(self):
         """Host (pinned) -> device copies of every per-segment input; returns bytes moved."""
@@ -86,7 +87,8 @@ class BafGridDevice:
         ic1 = ce.size if ic1 is None else ic1
         pc, pv = _priors(priors_table, CNt_min, CNt_max)
         L = _lib.lib()
-        need = L.sqz_baf_grid_workspace_bytes(self.N, self.S, pl.size, ic1 - ic0)
+        need = L.sqz_baf_grid_workspace_preferred_bytes(
+            self.N, self.S, pl.size, ic1 - ic0, int(CNt_max) - int(CNt_min) + 1, self.ws_cap)
         if self._ws is None or self._ws.numel() < need + 256:
             self._ws = torch.empty(need + 256, dtype=torch.uint8, device=self.device)
         base = self._ws.data_ptr()
