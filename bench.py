@@ -298,15 +298,20 @@ def run_ours(args, rank, world, local_rank):
     fast_ms = ms3[1] / max(ncall.value, 1)
     local_evals = float(c1 - c0) * nP * n
     padded = float(nPT * PT) / nP  # ragged last ploidy tile is computed and discarded
-    # executed fp64-pipe work per evaluation of the factorised kernel:
-    inst = 4.0 * n_c + 1 + (2.0 * T + 2.0 * n_c) / PT      # DFMA/DMUL/DSETP issue slots
-    flop = 6.0 * n_c + 1 + (3.0 * T + 3.0 * n_c) / PT      # DFMA = 2 flops, others 1
+    # Executed work per evaluation of the split kernel.  Per (copy number,
+    # ploidy): 2 DFMA + DSETP on the fp64 pipe and 2 FSEL; per copy number 2 DMUL; per
+    # ploidy 1 DMUL; the per-column pre-pass (2 T compares + ~14 n_c for sqrt and scaling)
+    # is shared by all nP ploidies of a column.
+    pre = (2.0 * T + 14.0 * n_c) / nP
+    inst = 3.0 * n_c + 1 + 2.0 * n_c / PT + pre             # fp64-pipe issue slots
+    math = inst + 2.0 * n_c                                 # + the FSEL pair of each minimum
+    flop = 5.0 * n_c + 1 + 2.0 * n_c / PT + 1.5 * pre       # DFMA = 2 flops, others 1
     ach = local_evals * flop / (fast_ms * 1e-3) / 1e12 if fast_ms > 0 else None
     # reference formulation: 11 n_c + 13 T flops and n_c + T logs per eval
     ref_flops = 11.0 * n_c + 13.0 * T
     ref_logs = n_c + T
     roofline = {
-        "bound": "fp64", "kernel": "baf_grid_fast_kernel<%d,false>" % PT,
+        "bound": "fp64", "kernel": "baf_grid_split_kernel<%d,false> (+ baf_colterm pre-pass)" % PT,
         "achieved": ach, "peak": peak.value, "unit": "TFLOP/s",
         "frac": (ach / peak.value) if ach and peak.value else None,
         "peak_source": "measured live: sqz_fp64_peak, dependent-free DFMA chains on all "
@@ -315,6 +320,12 @@ def run_ours(args, rank, world, local_rank):
         "fp64_issue_slots_per_eval": inst, "flops_per_eval_executed": flop,
         "pipe_util": (local_evals * inst / (fast_ms * 1e-3)) / (peak.value * 1e12 / 2)
         if fast_ms > 0 and peak.value else None,
+        "math_issue_slots_per_eval": math,
+        "math_dispatch_util": (local_evals * math / (fast_ms * 1e-3)) / (peak.value * 1e12 / 2)
+        if fast_ms > 0 and peak.value else None,
+        "math_dispatch_note": "on B200 every warp-wide math instruction (fp64 or the FSEL "
+                              "pair of a minimum) holds the SMSP math dispatch ~2.2 cycles "
+                              "(tools/microbench*.cu); this is the binding resource",
         "tile_padding": padded,
         "reference_formulation": {
             "flops_per_eval": ref_flops, "logs_per_eval": ref_logs,
@@ -342,9 +353,10 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "sqz_baf_grid (host pointers)" if world == 1 else
                        "BafGridDevice.upload + sqz_baf_grid_dev + NCCL all-gather + D2H"},
-        "gpu_launches": 4 * args.steps,
-        "gpu_launches_note": "per step: baf_prep, baf_grid_fast, baf_grid_finalize, "
-                             "baf_grid_faithful (repair); + torch copy kernels for N>1",
+        "gpu_launches": 5 * args.steps,
+        "gpu_launches_note": "per step: baf_prep, baf_colterm, baf_grid_split, "
+                             "baf_grid_finalize, baf_grid_faithful (repair), per column "
+                             "batch; + torch copy kernels for N>1",
         "roofline": roofline,
         "fit_wall_ms": e2e_ms,
         "solution": {"cellularity": float(ce[int(np.argmax(lpp_sum)) // nP]) if world == 1 else None,

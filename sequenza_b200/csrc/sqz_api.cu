@@ -170,6 +170,13 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
                          prior_value, n_prior, ratio_priority, mode, c->ws, c->ws_cap, c->st,
                          (double*)c->out);
     if (rc) return rc;
+  }
+  // Results are copied only after every device has its work queued: a device-to-host
+  // copy into pageable memory blocks the calling thread until that device is done.
+  for (int d = 0; d < ndev; ++d) {
+    DevCtx* c = &g_ctx[d];
+    const int64_t nCs = c0[d + 1] - c0[d];
+    SQZ_CUDA(cudaSetDevice(d));
     // device slice [S][nCs*nP] -> host [S][G] at column offset c0*nP
     SQZ_CUDA(cudaMemcpy2DAsync(out + c0[d] * nP, (size_t)G * 8, c->out, (size_t)(nCs * nP) * 8,
                                (size_t)(nCs * nP) * 8, (size_t)S, cudaMemcpyDeviceToHost,
@@ -437,8 +444,12 @@ int sqz_mufreq_grid(const double* mufreq, const double* depth_ratio,
                             c0[d + 1], avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN,
                             prior_value, n_prior, c->ws, c->ws_cap, c->st, (double*)c->out);
     if (rc) return rc;
-    SQZ_CUDA(cudaMemcpyAsync(lpp_sum_out + c0[d] * nP, c->out, (size_t)(nCs * nP) * 8,
-                             cudaMemcpyDeviceToHost, c->st));
+  }
+  for (int d = 0; d < ndev; ++d) {  // copy back only after all devices have been queued
+    const int64_t nCs = c0[d + 1] - c0[d];
+    SQZ_CUDA(cudaSetDevice(d));
+    SQZ_CUDA(cudaMemcpyAsync(lpp_sum_out + c0[d] * nP, g_ctx[d].out, (size_t)(nCs * nP) * 8,
+                             cudaMemcpyDeviceToHost, g_ctx[d].st));
   }
   for (int d = 0; d < ndev; ++d) {
     SQZ_CUDA(cudaSetDevice(d));
