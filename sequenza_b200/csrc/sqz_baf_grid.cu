@@ -777,7 +777,19 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
                          baf_split_supported(m.nc, g.PT, g.threads) &&
                          cw_bytes >= baf_split_column_bytes(m.nc, N_total);
   if (use_split) {
-    rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st);
+    // candidate pruning relies on the residual being monotone over a ploidy tile
+    bool mono_up = true, mono_dn = true;
+    for (int64_t i = 1; i < nP; ++i) {
+      if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
+      if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
+    }
+    // Measured on B200: with few copy numbers (config 3, 8 of them) pruning wins 1.6x; with
+    // many (config 2, 21) the per-thread bound pass and the divergence cost more than the
+    // skipped work saves, so the plain split kernel is used.  SQZ_PRUNE=0/1 overrides.
+    const int prune_env = env_int("SQZ_PRUNE", -1);
+    const bool prune = (mono_up || mono_dn) && (prune_env < 0 ? m.nc <= 12 : prune_env != 0);
+    rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st,
+                       prune);
     if (rc) return rc;
   } else {
     const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;

@@ -254,6 +254,199 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   }
 }
 
+// ---- grid kernel with exact candidate pruning (plain mode, few copy numbers) -------------
+// For one segment and one ploidy tile only a few copy numbers can be the minimiser.  Over a
+// tile of sorted ploidies (checked on the host) the scaled ratio residual x_cj of copy
+// number c is monotone in j, so it sweeps [xm_c - h_c, xm_c + h_c] (midpoint and half-width
+// from the first and last table entries of the row), and
+//     q_cj = wub_c (1 + x_cj^2)  >=  LB_c := wub_c (1 + max(|xm_c| - h_c, 0)^2).
+// Each thread (a) computes LB_c for every copy number, (b) evaluates the one with the
+// smallest bound over the whole tile, (c) takes Qmax >= max_j qmin_j, and (d) evaluates only
+// the copy numbers with LB_c < Qmax (1 + 1e-12).  A copy number that is skipped has
+// q_cj >= LB_c >= qmin_j for every j, so it cannot lower any minimum: the result equals
+// evaluating all of them.  Candidates differ per thread; the rows of the model table are
+// padded by two doubles so that threads reading different rows hit different banks.
+template <int PT>
+__global__ void __launch_bounds__(128, 2)
+baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
+                       int nCb, int64_t N_total, double* __restrict__ partM,
+                       long long* __restrict__ partE) {
+  constexpr int LS = PT + 2;  // padded row stride of the log-ratio table
+  extern __shared__ __align__(16) double sm[];
+  const int nthr = blockDim.x, tid = threadIdx.x;
+  double* lmr = sm;                                                  // [nc][LS]
+  double* lmid = sm + m.nc * LS;                                     // [nc] row midpoint
+  double* lhw = lmid + m.nc;                                         // [nc] row half-width
+  double2* stage =
+      reinterpret_cast<double2*>(sm + m.nc * LS + 2 * ((m.nc + 1) & ~1));  // [2][nc][nthr]
+  double* LBc = reinterpret_cast<double*>(stage + 2 * m.nc * nthr);  // [nc][nthr]
+  int* Ec = reinterpret_cast<int*>(LBc + m.nc * nthr);              // [PT][nthr]
+  __shared__ double redM[4][PT];
+  __shared__ long long redE[4][PT];
+  __shared__ unsigned redBad[4];
+
+  int64_t b = blockIdx.x;
+  const int pt = (int)(b % a.nPT);
+  b /= a.nPT;
+  const int icl = (int)(b % nCb);
+  b /= nCb;
+  const int chunk = (int)(b % a.nChunk);
+  const int64_t smp = b / a.nChunk;
+  const int ic = ic0 + icl;
+  const int p0 = pt * PT;
+
+  const double cell = a.cell[ic];
+  const double adr = a.adr[smp];
+  for (int i = tid; i < m.nc * PT; i += nthr) {
+    const int c = i / PT, j = i - c * PT;
+    const int ip = min(p0 + j, a.nP - 1);  // ragged last tile repeats the last ploidy
+    lmr[c * LS + j] = log(theoretical_depth_ratio((double)(m.CNt_min + c), cell, a.ploidy[ip],
+                                                  (double)m.CNn, adr));
+  }
+#pragma unroll
+  for (int j = 0; j < PT; ++j) Ec[j * nthr + tid] = 0;
+  __syncthreads();
+  for (int c = tid; c < m.nc; c += nthr) {
+    const double f = lmr[c * LS], l = lmr[c * LS + PT - 1];
+    lmid[c] = 0.5 * (f + l);
+    lhw[c] = fabs(0.5 * (f - l));
+  }
+  __syncthreads();
+
+  const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
+  const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
+  const int64_t cb = s0 + (int64_t)chunk * per;
+  const int64_t ce = min(cb + per, s1);
+  const double2* cwc = cw + (int64_t)icl * m.nc * N_total;
+
+  double P[PT];
+#pragma unroll
+  for (int j = 0; j < PT; ++j) P[j] = 1.0;
+  unsigned bad = 0;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+
+  auto issue = [&](int buf, int64_t seg) {
+    double2* dst = stage + (buf * m.nc) * nthr + tid;
+    const double2* src = cwc + seg;
+    for (int c = 0; c < m.nc; ++c, dst += nthr, src += N_total) cp_async16(dst, src);
+    cp_async_commit();
+  };
+
+  int64_t s = cb + tid;
+  double2 rk_n = make_double2(0., 0.);
+  if (s < ce) {
+    rk_n = a.rk[s];
+    issue(0, s);
+  }
+  int it = 0, buf = 0;
+  while (s < ce) {
+    const double2 rk = rk_n;
+    const int64_t sn = s + nthr;
+    if (sn < ce) {
+      rk_n = a.rk[sn];
+      issue(buf ^ 1, sn);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    const double2* col = stage + (buf * m.nc) * nthr + tid;
+
+    // (a) lower bounds; the argmin only has to be a good guess, so it is taken on the
+    // high words with the copy-number index packed into the low six bits
+    const double akr = fabs(rk.x);
+    unsigned kbest = 0xFFFFFFFFu;
+    for (int c = 0; c < m.nc; ++c) {
+      double t = fabs(fma(lmid[c], rk.x, rk.y)) - lhw[c] * akr;
+      if (t < 0.0) t = 0.0;
+      const double wv = col[c * nthr].x;
+      const double lb = fma(wv, t * t, wv);
+      LBc[c * nthr + tid] = lb;
+      kbest = min(kbest, ((unsigned)__double2hiint(lb) & 0xFFFFFFC0u) | (unsigned)c);
+    }
+    const int first = (int)(kbest & 63u) < m.nc ? (int)(kbest & 63u) : 0;
+
+    double qmin[PT];
+#pragma unroll
+    for (int j = 0; j < PT; ++j) qmin[j] = INF;
+    auto eval = [&](int c) {
+      const double2 cwv = col[c * nthr];
+      const double* l = lmr + c * LS;
+      const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const double x = fma(l[j], krw, erw);
+        const double q = fma(x, x, cwv.x);
+        if (q < qmin[j]) qmin[j] = q;  // strict <, NaN never wins
+      }
+    };
+    // (b) most promising copy number, (c) Qmax: largest high word plus one step of 2^-20
+    eval(first);
+    unsigned qh = 0;
+#pragma unroll
+    for (int j = 0; j < PT; ++j) qh = max(qh, (unsigned)__double2hiint(qmin[j]));
+    const double qmax = qh >= 0x7FF00000u ? INF : __hiloint2double((int)(qh + 1u), 0);
+    // (d) the copy numbers that can still lower a minimum
+    unsigned long long need = 0;
+    for (int c = 0; c < m.nc; ++c)
+      if (LBc[c * nthr + tid] < qmax) need |= 1ull << c;
+    need &= ~(1ull << first);
+    while (need) {  // per-thread trip count; the warp runs as long as its slowest lane
+      const int c = __ffsll((long long)need) - 1;
+      need &= need - 1;
+      eval(c);
+    }
+
+#pragma unroll
+    for (int j = 0; j < PT; ++j) P[j] *= qmin[j];
+    if ((++it & 7) == 0) {  // q < 2^127 is ample; an overflow is flagged and repaired
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+        if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+        Ec[j * nthr + tid] += (hi >> 20) - 1023;
+        P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+      }
+    }
+    s = sn;
+    buf ^= 1;
+  }
+
+  const int lane = tid & 31, warp = tid >> 5, nwarp = (nthr + 31) >> 5;
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+    if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+    double v = log(__hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo));
+    long long e = (long long)Ec[j * nthr + tid] + ((hi >> 20) - 1023);
+    for (int off = 16; off; off >>= 1) {
+      v += __shfl_xor_sync(0xffffffffu, v, off);
+      e += __shfl_xor_sync(0xffffffffu, e, off);
+    }
+    if (lane == 0) {
+      redM[warp][j] = v;
+      redE[warp][j] = e;
+    }
+  }
+  for (int off = 16; off; off >>= 1) bad |= __shfl_xor_sync(0xffffffffu, bad, off);
+  if (lane == 0) redBad[warp] = bad;
+  __syncthreads();
+  if (tid < PT && p0 + tid < a.nP) {
+    double v = 0.;
+    long long e = 0;
+    unsigned bd = 0;
+    for (int w = 0; w < nwarp; ++w) {
+      v += redM[w][tid];
+      e += redE[w][tid];
+      bd |= redBad[w];
+    }
+    if ((bd >> tid) & 1u) v = __longlong_as_double(0x7FF8000000000000LL);
+    const int64_t Gs = (int64_t)a.nCs * a.nP;
+    const int64_t o = ((int64_t)chunk * a.S + smp) * Gs + (int64_t)ic * a.nP + p0 + tid;
+    partM[o] = v;
+    partE[o] = e;
+  }
+}
+
 // ---- host side ---------------------------------------------------------------------------
 size_t baf_split_column_bytes(int nc, int64_t N_total) {
   return (size_t)nc * (size_t)(N_total > 0 ? N_total : 1) * sizeof(double2);
@@ -262,6 +455,27 @@ size_t baf_split_column_bytes(int nc, int64_t N_total) {
 static size_t split_smem_bytes(int nc, int PT, int threads) {
   return (size_t)nc * PT * sizeof(double) + (size_t)2 * nc * threads * sizeof(double2) +
          (size_t)PT * threads * sizeof(int);
+}
+
+static size_t pruned_smem_bytes(int nc, int PT, int threads) {
+  return (size_t)(nc * (PT + 2) + 2 * ((nc + 1) & ~1)) * sizeof(double) +
+         (size_t)2 * nc * threads * sizeof(double2) + (size_t)nc * threads * sizeof(double) +
+         (size_t)PT * threads * sizeof(int);
+}
+
+template <int PT>
+static int launch_pruned(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
+                         const double2* cw, int ic0, int nCb, double* partM, long long* partE,
+                         cudaStream_t st) {
+  const size_t smb = pruned_smem_bytes(m.nc, PT, threads);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
+  if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
+  baf_grid_pruned_kernel<PT><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb, N_total,
+                                                                  partM, partE);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
 }
 
 bool baf_split_supported(int nc, int PT, int threads) {
@@ -286,11 +500,13 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
 // Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st) {
+                  cudaStream_t st, bool prune) {
+  if (prune && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = false;
   const size_t per_col = baf_split_column_bytes(m.nc, N_total);
   int64_t nCb_max = (int64_t)(cw_bytes / per_col);
   if (nCb_max < 1) return fail(SQZ_ERR_SIZE, "split path needs room for one column");
   if (nCb_max > a.nCs) nCb_max = a.nCs;
+  if (nCb_max > 65535) nCb_max = 65535;
   double2* cw = (double2*)cw_buf;
   const bool rp = a.rp != 0;
   for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += nCb_max) {
@@ -300,6 +516,13 @@ int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, i
                                                                         cw);
     SQZ_CUDA(cudaGetLastError());
     int rc;
+    if (prune) {
+      if (PT == 8) rc = launch_pruned<8>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
+      else if (PT == 16) rc = launch_pruned<16>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
+      else rc = launch_pruned<32>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
+      if (rc) return rc;
+      continue;
+    }
 #define SQZ_SPLIT(PTV)                                                                     \
   rc = rp ? launch_split<PTV, true>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st) \
           : launch_split<PTV, false>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st)
