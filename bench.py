@@ -231,6 +231,9 @@ def run_ours(args, rank, world, local_rank):
     t1 = time.perf_counter()
     ms3 = (C.c_double * 3)()
     ncall = C.c_int(0)
+    kpath = C.c_int(0)
+    n_cand = C.c_ulonglong(0)
+    L.sqz_profile_counters(C.byref(kpath), C.byref(n_cand))
     L.sqz_profile_collect(ms3, C.byref(ncall))
     L.sqz_profile_enable(0)
     clocks = sampler.finish(t0, t1)
@@ -298,20 +301,34 @@ def run_ours(args, rank, world, local_rank):
     fast_ms = ms3[1] / max(ncall.value, 1)
     local_evals = float(c1 - c0) * nP * n
     padded = float(nPT * PT) / nP  # ragged last ploidy tile is computed and discarded
-    # Executed work per evaluation of the split kernel.  Per (copy number,
-    # ploidy): 2 DFMA + DSETP on the fp64 pipe and 2 FSEL; per copy number 2 DMUL; per
+    # Executed work per evaluation.  Per evaluated (copy number, ploidy):
+    # 2 DFMA + DSETP on the fp64 pipe and 2 FSEL; per evaluated copy number 2 DMUL; per
     # ploidy 1 DMUL; the per-column pre-pass (2 T compares + ~14 n_c for sqrt and scaling)
-    # is shared by all nP ploidies of a column.
+    # is shared by all nP ploidies of a column.  The split kernel evaluates every copy
+    # number; the pruned kernel only those its bounds cannot exclude (counted by the
+    # kernel itself while profiling) plus ~6 fp64 / ~4 integer instructions per copy number
+    # and tile for the bounds.
     pre = (2.0 * T + 14.0 * n_c) / nP
-    inst = 3.0 * n_c + 1 + 2.0 * n_c / PT + pre             # fp64-pipe issue slots
-    math = inst + 2.0 * n_c                                 # + the FSEL pair of each minimum
-    flop = 5.0 * n_c + 1 + 2.0 * n_c / PT + 1.5 * pre       # DFMA = 2 flops, others 1
+    kernel_names = {0: "baf_grid_fast_kernel (fused)", 1: "baf_grid_split_kernel",
+                    2: "baf_grid_pruned_kernel"}
+    if kpath.value == 2 and ncall.value > 0:
+        cand = n_cand.value / (float(ncall.value) * n * (c1 - c0) * nPT)  # per segment, tile
+        inst = cand * (3.0 + 2.0 / PT) + 1 + 6.0 * n_c / PT + pre
+        math = inst + cand * 2.0 + 4.0 * n_c / PT
+        flop = cand * (5.0 + 2.0 / PT) + 1 + 8.0 * n_c / PT + 1.5 * pre
+    else:
+        cand = float(n_c)
+        inst = 3.0 * n_c + 1 + 2.0 * n_c / PT + pre         # fp64-pipe issue slots
+        math = inst + 2.0 * n_c                             # + the FSEL pair of each minimum
+        flop = 5.0 * n_c + 1 + 2.0 * n_c / PT + 1.5 * pre   # DFMA = 2 flops, others 1
     ach = local_evals * flop / (fast_ms * 1e-3) / 1e12 if fast_ms > 0 else None
     # reference formulation: 11 n_c + 13 T flops and n_c + T logs per eval
     ref_flops = 11.0 * n_c + 13.0 * T
     ref_logs = n_c + T
     roofline = {
-        "bound": "fp64", "kernel": "baf_grid_split_kernel<%d,false> (+ baf_colterm pre-pass)" % PT,
+        "bound": "fp64",
+        "kernel": "%s<%d> (+ baf_colterm pre-pass)" % (kernel_names.get(kpath.value, "?"), PT),
+        "copy_numbers_evaluated_per_segment_and_tile": cand, "copy_numbers": n_c,
         "achieved": ach, "peak": peak.value, "unit": "TFLOP/s",
         "frac": (ach / peak.value) if ach and peak.value else None,
         "peak_source": "measured live: sqz_fp64_peak, dependent-free DFMA chains on all "

@@ -51,6 +51,7 @@ SIGNATURES = {
     "sqz_baf_grid_plan": (_i, [_i64, _i64, _i64, _i64, _i, _i, _i, _i, _p]),
     "sqz_profile_enable": (_i, [_i]),
     "sqz_profile_collect": (_i, [_p, _p]),
+    "sqz_profile_counters": (_i, [_p, _p]),
 }
 
 _lib = None

@@ -40,6 +40,7 @@ int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_m
                   int CNn, int ratio_priority, int* out5);
 int profile_enable(int on);
 int profile_collect(double* ms3, int* n_calls);
+int profile_counters(int* path, unsigned long long* n_eval);
 size_t mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nCs);
 int mufreq_point_launch(const double* d_F, const double* d_ratio, const double* d_wm,
                         const double* d_wr, int64_t N, double cellularity, double ploidy,
@@ -475,6 +476,9 @@ int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, 
 
 int sqz_profile_enable(int on) { return profile_enable(on); }
 int sqz_profile_collect(double* ms3, int* n_calls) { return profile_collect(ms3, n_calls); }
+int sqz_profile_counters(int* path, unsigned long long* n_eval) {
+  return profile_counters(path, n_eval);
+}
 
 int sqz_fp64_peak(int device, int repeats, double* tflops_out) {
   if (!tflops_out) return fail(SQZ_ERR_ARG, "tflops_out is null");

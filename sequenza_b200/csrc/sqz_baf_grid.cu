@@ -486,6 +486,8 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 // has synchronised.  Off by default; bench.py turns it on for the roofline numbers.
 struct ProfSet {
   cudaEvent_t ev[4];
+  int path = 0;                    // 0 fused, 1 split, 2 split + candidate pruning
+  unsigned long long n_eval = 0;   // (segment, tile, copy number) evaluations, pruned path
 };
 static bool g_prof_on = false;
 static int g_prof_dev = -1;
@@ -518,7 +520,25 @@ static ProfSet* prof_next() {
       if (cudaEventCreate(&p.ev[k]) != cudaSuccess) return nullptr;
     g_prof->push_back(p);
   }
-  return &(*g_prof)[g_prof_n++];
+  ProfSet* r = &(*g_prof)[g_prof_n++];
+  r->path = 0;
+  r->n_eval = 0;
+  return r;
+}
+
+// kernel path and candidate-evaluation count of the calls recorded since profile_enable(1)
+// (read before profile_collect resets them; the caller has synchronised)
+int profile_counters(int* path, unsigned long long* n_eval) {
+  int p = 0;
+  unsigned long long n = 0;
+  if (g_prof)
+    for (int i = 0; i < g_prof_n; ++i) {
+      p = (*g_prof)[i].path;
+      n += (*g_prof)[i].n_eval;
+    }
+  if (path) *path = p;
+  if (n_eval) *n_eval = n;
+  return SQZ_OK;
 }
 
 // sums (ms) of prep / fast kernel / finalize+repair over the calls recorded since
@@ -628,6 +648,7 @@ struct Workspace {
   double* partM;
   long long* partE;
   int *fix_list, *fix_count;
+  unsigned long long* stats;  // candidate evaluations of the pruned kernel (profiling only)
   size_t bytes;
 };
 
@@ -658,6 +679,7 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   w.partE = (long long*)take(items * (size_t)want * sizeof(long long));
   w.fix_list = (int*)take(items * sizeof(int));
   w.fix_count = (int*)take(sizeof(int));
+  w.stats = (unsigned long long*)take(sizeof(unsigned long long));
   w.bytes = off;
   return w;
 }
@@ -788,8 +810,14 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     // skipped work saves, so the plain split kernel is used.  SQZ_PRUNE=0/1 overrides.
     const int prune_env = env_int("SQZ_PRUNE", -1);
     const bool prune = (mono_up || mono_dn) && (prune_env < 0 ? m.nc <= 12 : prune_env != 0);
+    if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
     rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st,
-                       prune);
+                       prune, prof ? w.stats : nullptr);
+    if (prof) {
+      prof->path = prune ? 2 : 1;
+      SQZ_CUDA(cudaMemcpyAsync(&prof->n_eval, w.stats, sizeof(unsigned long long),
+                               cudaMemcpyDeviceToHost, st));
+    }
     if (rc) return rc;
   } else {
     const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;

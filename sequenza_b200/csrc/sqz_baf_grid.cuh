@@ -27,6 +27,6 @@ size_t baf_split_column_bytes(int nc, int64_t N_total);
 bool baf_split_supported(int nc, int PT, int threads);
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, bool prune);
+                  cudaStream_t st, bool prune, unsigned long long* stats);
 
 }  // namespace sqz

@@ -270,7 +270,7 @@ template <int PT>
 __global__ void __launch_bounds__(128, 2)
 baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
                        int nCb, int64_t N_total, double* __restrict__ partM,
-                       long long* __restrict__ partE) {
+                       long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int LS = PT + 2;  // padded row stride of the log-ratio table
   extern __shared__ __align__(16) double sm[];
   const int nthr = blockDim.x, tid = threadIdx.x;
@@ -323,6 +323,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
 #pragma unroll
   for (int j = 0; j < PT; ++j) P[j] = 1.0;
   unsigned bad = 0;
+  unsigned n_eval = 0;  // copy numbers this thread evaluated (reported when profiling)
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
   auto issue = [&](int buf, int64_t seg) {
@@ -390,6 +391,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     for (int c = 0; c < m.nc; ++c)
       if (LBc[c * nthr + tid] < qmax) need |= 1ull << c;
     need &= ~(1ull << first);
+    n_eval += 1u + (unsigned)__popcll(need);
     while (need) {  // per-thread trip count; the warp runs as long as its slowest lane
       const int c = __ffsll((long long)need) - 1;
       need &= need - 1;
@@ -429,6 +431,10 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   }
   for (int off = 16; off; off >>= 1) bad |= __shfl_xor_sync(0xffffffffu, bad, off);
   if (lane == 0) redBad[warp] = bad;
+  if (stats) {
+    for (int off = 16; off; off >>= 1) n_eval += __shfl_xor_sync(0xffffffffu, n_eval, off);
+    if (lane == 0) atomicAdd(stats, (unsigned long long)n_eval);
+  }
   __syncthreads();
   if (tid < PT && p0 + tid < a.nP) {
     double v = 0.;
@@ -466,14 +472,14 @@ static size_t pruned_smem_bytes(int nc, int PT, int threads) {
 template <int PT>
 static int launch_pruned(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
                          const double2* cw, int ic0, int nCb, double* partM, long long* partE,
-                         cudaStream_t st) {
+                         unsigned long long* stats, cudaStream_t st) {
   const size_t smb = pruned_smem_bytes(m.nc, PT, threads);
   SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
   baf_grid_pruned_kernel<PT><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb, N_total,
-                                                                  partM, partE);
+                                                                  partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
@@ -500,7 +506,7 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
 // Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, bool prune) {
+                  cudaStream_t st, bool prune, unsigned long long* stats) {
   if (prune && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = false;
   const size_t per_col = baf_split_column_bytes(m.nc, N_total);
   int64_t nCb_max = (int64_t)(cw_bytes / per_col);
@@ -517,9 +523,9 @@ int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, i
     SQZ_CUDA(cudaGetLastError());
     int rc;
     if (prune) {
-      if (PT == 8) rc = launch_pruned<8>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
-      else if (PT == 16) rc = launch_pruned<16>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
-      else rc = launch_pruned<32>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st);
+      if (PT == 8) rc = launch_pruned<8>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
+      else if (PT == 16) rc = launch_pruned<16>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
+      else rc = launch_pruned<32>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
       if (rc) return rc;
       continue;
     }

@@ -271,3 +271,33 @@ def test_full_size_properties_config2():
     ci = S.get_ci(fit)
     assert abs(ci["max.cellularity"] - 0.7) <= 0.011 and abs(ci["max.ploidy"] - 2.4) <= 0.11
     np.testing.assert_array_equal(S.baf_grid_sums(**baf_args(seg), **kw), s1)
+
+
+def test_grid_kernel_paths_agree(oracle, monkeypatch):
+    """The three fast-path kernels (fused, split, split + candidate pruning) and the
+    orderings of the ploidy axis that switch pruning off must all give the oracle's sums."""
+    seg = synth_segments(3000, seed=88)
+    ce, pl = S.r_seq(0.1, 1, 0.02), S.r_seq(1, 7, 0.05)
+    kw = dict(cellularity=ce, priors_table=PRI, **baf_args(seg))
+    ref = oracle.baf_grid_sums(ploidy=pl, **kw)
+    for env in ({"SQZ_SPLIT": "0"}, {"SQZ_PRUNE": "0"}, {"SQZ_PRUNE": "1"},
+                {"SQZ_PRUNE": "1", "SQZ_PT": "16"}, {"SQZ_PRUNE": "1", "SQZ_PT": "8"}):
+        for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        got = S.baf_grid_sums(ploidy=pl, **kw)
+        assert rel_close(got, ref), env
+        assert int(np.argmax(got)) == int(np.argmax(ref)), env
+    for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT"):
+        monkeypatch.delenv(k, raising=False)
+    # descending and unsorted ploidy vectors (pruning needs a monotone tile; unsorted input
+    # falls back to the plain split kernel), duplicated values
+    for p2 in (pl[::-1].copy(), np.random.default_rng(1).permutation(pl),
+               np.concatenate([pl[:5], pl[:5]])):
+        got = S.baf_grid_sums(ploidy=p2, **kw)
+        assert rel_close(got, oracle.baf_grid_sums(ploidy=p2, **kw))
+    # CNt.max = 20 with pruning forced on (many copy numbers, per-thread candidates)
+    monkeypatch.setenv("SQZ_PRUNE", "1")
+    kw20 = dict(kw, CNt_max=20)
+    assert rel_close(S.baf_grid_sums(ploidy=pl, **kw20), oracle.baf_grid_sums(ploidy=pl, **kw20))
