@@ -182,6 +182,26 @@ int sqz_mufreq_point_dev(const double* d_mufreq, const double* d_depth_ratio,
                          const double* prior_CN, const double* prior_value, int n_prior,
                          void* stream, double* d_out);
 
+/* B3 with scalar weights, as sequenza.results calls it (weight.mufreq = weight.ratio = 100,
+ * R/results.R:153-157): the N x 4 result depends on round(F * w.m) and
+ * round(w.r * r/(1+r)) only, so the (w.r+1) x (w.m+1) answers are computed once with the
+ * same arithmetic and every position becomes a lookup (16 bytes in, 32 bytes out).
+ * Weights must be non-negative integers <= 4096 with (w.m+1)(w.r+1) <= 4e6, otherwise
+ * SQZ_ERR_ARG (use sqz_mufreq_point).  The _dev form needs a device buffer of
+ * sqz_mufreq_scalar_table_bytes(...) bytes, 32-byte aligned. */
+size_t sqz_mufreq_scalar_table_bytes(double weight_mufreq, double weight_ratio);
+int sqz_mufreq_point_scalar(const double* mufreq, const double* depth_ratio, int64_t N,
+                            double weight_mufreq, double weight_ratio, double cellularity,
+                            double ploidy, double avg_depth_ratio, int CNt_min, int CNt_max,
+                            int CNn, const double* prior_CN, const double* prior_value,
+                            int n_prior, double* out);
+int sqz_mufreq_point_scalar_dev(const double* d_mufreq, const double* d_depth_ratio, int64_t N,
+                                double weight_mufreq, double weight_ratio, double cellularity,
+                                double ploidy, double avg_depth_ratio, int CNt_min, int CNt_max,
+                                int CNn, const double* prior_CN, const double* prior_value,
+                                int n_prior, void* d_table, size_t table_bytes, void* stream,
+                                double* d_out);
+
 /* ---------------------------------------------------------------------------------
  * B4  mufreq.model.fit grid -- replaces fit.cp + pblapply, R/bayes.R:179-185.
  * Same output convention as sqz_baf_grid.

@@ -39,6 +39,11 @@ SIGNATURES = {
     "sqz_baf_point_dev": (_i, [_p] * 6 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _i, _p,
                                _p]),
     "sqz_mufreq_point": (_i, [_p] * 4 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _p]),
+    "sqz_mufreq_scalar_table_bytes": (_sz, [_d, _d]),
+    "sqz_mufreq_point_scalar": (_i, [_p, _p, _i64, _d, _d, _d, _d, _d, _i, _i, _i, _p, _p, _i,
+                                     _p]),
+    "sqz_mufreq_point_scalar_dev": (_i, [_p, _p, _i64, _d, _d, _d, _d, _d, _i, _i, _i, _p, _p,
+                                         _i, _p, _sz, _p, _p]),
     "sqz_mufreq_point_dev": (_i, [_p] * 4 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _p,
                                   _p]),
     "sqz_mufreq_grid": (_i, [_p] * 4 + [_i64, _p, _i64, _p, _i64, _d, _i, _i, _i, _p, _p,

@@ -164,12 +164,22 @@ def mufreq_bayes(mufreq, depth_ratio, cellularity, ploidy, avg_depth_ratio,
     """R/bayes.R:126-173 -> N x 4 array with columns CNn, CNt, Mt, LPP (R/bayes.R:171)."""
     f = _lib.vec(mufreq)
     n = f.size
+    pc, pv = _priors(priors_table, CNt_min, CNt_max)
+    out = np.empty((4, n))
+    L = _lib.lib()
+    if (np.ndim(weight_mufreq) == 0 and np.ndim(weight_ratio) == 0 and
+            L.sqz_mufreq_scalar_table_bytes(float(weight_mufreq), float(weight_ratio)) > 0):
+        # scalar weights (the reference's defaults): table-driven streaming kernel
+        r = _lib.vec(depth_ratio, n, "depth.ratio")
+        _lib.check(L.sqz_mufreq_point_scalar(
+            _lib.ptr(f), _lib.ptr(r), n, float(weight_mufreq), float(weight_ratio),
+            float(cellularity), float(ploidy), float(avg_depth_ratio), int(CNt_min),
+            int(CNt_max), int(CNn), _lib.ptr(pc), _lib.ptr(pv), pc.size, _lib.ptr(out)))
+        return out.T.copy()
     v = [_lib.vec(a, n, nm) for a, nm in ((f, "mufreq"), (depth_ratio, "depth.ratio"),
                                           (weight_mufreq, "weight.mufreq"),
                                           (weight_ratio, "weight.ratio"))]
-    pc, pv = _priors(priors_table, CNt_min, CNt_max)
-    out = np.empty((4, n))
-    _lib.check(_lib.lib().sqz_mufreq_point(
+    _lib.check(L.sqz_mufreq_point(
         *[_lib.ptr(a) for a in v], n, float(cellularity), float(ploidy),
         float(avg_depth_ratio), int(CNt_min), int(CNt_max), int(CNn), _lib.ptr(pc),
         _lib.ptr(pv), pc.size, _lib.ptr(out)))

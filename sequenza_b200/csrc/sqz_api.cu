@@ -53,6 +53,12 @@ int mufreq_grid_launch(const double* d_F, const double* d_ratio, const double* d
                        int CNt_min, int CNt_max, int CNn, const double* prior_CN,
                        const double* prior_value, int n_prior, void* workspace,
                        size_t workspace_bytes, cudaStream_t st, double* d_out);
+size_t mufreq_scalar_table_bytes(double wm, double wr);
+int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t N, double wm,
+                               double wr, double cellularity, double ploidy, double adr,
+                               int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                               const double* prior_value, int n_prior, void* table,
+                               size_t table_bytes, cudaStream_t st, double* d_out);
 int model_points_launch(int kind, double cellularity, double ploidy, double adr, int CNt_min,
                         int CNt_max, int CNn, const double* prior_CN,
                         const double* prior_value, int n_prior, int* T_out, double* h_out);
@@ -371,6 +377,46 @@ int sqz_mufreq_point(const double* mufreq, const double* depth_ratio,
     return mufreq_point_launch(dv[0], dv[1], dv[2], dv[3], N, cellularity, ploidy,
                                avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
                                n_prior, st, d_out);
+  });
+}
+
+size_t sqz_mufreq_scalar_table_bytes(double weight_mufreq, double weight_ratio) {
+  return mufreq_scalar_table_bytes(weight_mufreq, weight_ratio);
+}
+
+int sqz_mufreq_point_scalar_dev(const double* d_mufreq, const double* d_depth_ratio, int64_t N,
+                                double weight_mufreq, double weight_ratio, double cellularity,
+                                double ploidy, double avg_depth_ratio, int CNt_min, int CNt_max,
+                                int CNn, const double* prior_CN, const double* prior_value,
+                                int n_prior, void* d_table, size_t table_bytes, void* stream,
+                                double* d_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return mufreq_point_scalar_launch(d_mufreq, d_depth_ratio, N, weight_mufreq, weight_ratio,
+                                    cellularity, ploidy, avg_depth_ratio, CNt_min, CNt_max, CNn,
+                                    prior_CN, prior_value, n_prior, d_table, table_bytes,
+                                    (cudaStream_t)stream, d_out);
+}
+
+int sqz_mufreq_point_scalar(const double* mufreq, const double* depth_ratio, int64_t N,
+                            double weight_mufreq, double weight_ratio, double cellularity,
+                            double ploidy, double avg_depth_ratio, int CNt_min, int CNt_max,
+                            int CNn, const double* prior_CN, const double* prior_value,
+                            int n_prior, double* out) {
+  const size_t tbytes = mufreq_scalar_table_bytes(weight_mufreq, weight_ratio);
+  if (tbytes == 0)
+    return fail(SQZ_ERR_ARG, "scalar weights must be non-negative integers <= 4096 (use "
+                             "sqz_mufreq_point otherwise)");
+  const double* vec[2] = {mufreq, depth_ratio};
+  return point_host(2, vec, N, out, [&](const double** dv, cudaStream_t st, double* d_out) {
+    int cur = 0;
+    SQZ_CUDA(cudaGetDevice(&cur));
+    DevCtx& c = g_ctx[cur];
+    int rc = grow(&c.ws, &c.ws_cap, tbytes);
+    if (rc) return rc;
+    return mufreq_point_scalar_launch(dv[0], dv[1], N, weight_mufreq, weight_ratio, cellularity,
+                                      ploidy, avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN,
+                                      prior_value, n_prior, c.ws, c.ws_cap, st, d_out);
   });
 }
 

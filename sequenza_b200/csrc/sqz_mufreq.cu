@@ -273,4 +273,127 @@ int model_points_launch(int kind, double cellularity, double ploidy, double adr,
   return SQZ_OK;
 }
 
+// ---- scalar weights: the answer depends on two integers only ---------------------------
+// sequenza.results calls mufreq.bayes with the default scalar weights 100 / 100
+// (R/results.R:153-157).  Then the row of a position is a function of
+//   k_r = round(w.r * r/(1+r)) in 0..w.r   and   k_m = round(F * w.m) in 0..w.m
+// alone, so the (w.r+1) x (w.m+1) answers are computed once with the same nmath sequence
+// (mufreq_table_kernel, one thread per pair) and the per-position kernel becomes a
+// streaming lookup: 16 bytes in, 32 bytes out, HBM-bound.  Positions whose counts fall
+// outside the table (NA, negative ratio, F outside [0,1]) take the direct path.
+__global__ void __launch_bounds__(128)
+mufreq_table_kernel(int nr, int nm, double wr, double wm, double cell, double ploidy,
+                    double adr, CnModel m, double4* __restrict__ table) {
+  extern __shared__ double sm[];
+  double* probr = sm;
+  double* mm = sm + m.nc;
+  build_muf_model(m, cell, ploidy, adr, probr, mm);
+  __syncthreads();
+  const int64_t n = (int64_t)nr * nm;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int kr = (int)(i / nm), km = (int)(i - (int64_t)kr * nm);
+    const BinomHoist hr = binom_hoist((double)kr, wr), hm = binom_hoist((double)km, wm);
+    int kc, kt;
+    double lpp;
+    mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
+    table[i] = make_double4(kc >= 0 ? (double)m.CNn : na_real(),
+                            kc >= 0 ? (double)(m.CNt_min + kc) : na_real(),
+                            kc >= 0 ? (double)kt : na_real(), lpp);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+mufreq_lookup_kernel(int64_t N, const double* __restrict__ F, const double* __restrict__ ratio,
+                     int nr, int nm, double wr, double wm, double cell, double ploidy,
+                     double adr, CnModel m, const double4* __restrict__ table,
+                     double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* probr = sm;
+  double* mm = sm + m.nc;
+  build_muf_model(m, cell, ploidy, adr, probr, mm);  // for the rare direct path
+  __syncthreads();
+  // four positions per thread and iteration: all input loads, then all table lookups,
+  // then the stores, so that several memory requests are in flight per thread
+  constexpr int U = 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t s0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s0 < N; s0 += U * stride) {
+    double r[U], f[U], kr[U], km[U];
+    double4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t s = s0 + u * stride;
+      r[u] = s < N ? ratio[s] : 1.0;
+      f[u] = s < N ? F[s] : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      kr[u] = nearbyint(wr * (r[u] / (1 + r[u])));  // R/bayes.R:26
+      km[u] = nearbyint(f[u] * wm);                  // R/bayes.R:4
+      const bool in = kr[u] >= 0.0 && kr[u] < (double)nr && km[u] >= 0.0 && km[u] < (double)nm;
+      v[u] = table[in ? (int64_t)kr[u] * nm + (int64_t)km[u] : 0];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t s = s0 + u * stride;
+      if (s >= N) continue;
+      const bool in = kr[u] >= 0.0 && kr[u] < (double)nr && km[u] >= 0.0 && km[u] < (double)nm;
+      if (!in) {  // outside the table (NA, ratio < 0, F outside [0, 1]): direct evaluation
+        const BinomHoist hr = binom_hoist(kr[u], wr), hm = binom_hoist(km[u], wm);
+        int kc, kt;
+        double lpp;
+        mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
+        v[u] = make_double4(kc >= 0 ? (double)m.CNn : na_real(),
+                            kc >= 0 ? (double)(m.CNt_min + kc) : na_real(),
+                            kc >= 0 ? (double)kt : na_real(), lpp);
+      }
+      out[s] = v[u].x;
+      out[N + s] = v[u].y;
+      out[2 * N + s] = v[u].z;
+      out[3 * N + s] = v[u].w;
+    }
+  }
+}
+
+// number of table bytes sqz_mufreq_point_scalar_dev needs (0: weights not usable for the
+// table, the caller should use the vector-weight entry point)
+size_t mufreq_scalar_table_bytes(double wm, double wr) {
+  if (!(wm >= 0) || !(wr >= 0) || wm != nearbyint(wm) || wr != nearbyint(wr)) return 0;
+  if (wm > 4096 || wr > 4096 || (wm + 1) * (wr + 1) > 4.0e6) return 0;
+  return (size_t)((wm + 1) * (wr + 1)) * sizeof(double4);
+}
+
+int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t N, double wm,
+                               double wr, double cellularity, double ploidy, double adr,
+                               int CNt_min, int CNt_max, int CNn, const double* prior_CN,
+                               const double* prior_value, int n_prior, void* table,
+                               size_t table_bytes, cudaStream_t st, double* d_out) {
+  if (N < 0) return fail(SQZ_ERR_ARG, "negative N");
+  const size_t need = mufreq_scalar_table_bytes(wm, wr);
+  if (need == 0)
+    return fail(SQZ_ERR_ARG, "scalar weights must be non-negative integers <= 4096 (use the "
+                             "vector-weight entry point otherwise)");
+  if (!table || table_bytes < need || ((uintptr_t)table & 31))
+    return fail(SQZ_ERR_SIZE, "table buffer missing, misaligned or too small");
+  CnModel m;
+  int rc = build_cn_model(1, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
+                          nullptr);
+  if (rc) return rc;
+  if (N == 0) return SQZ_OK;
+  const int nr = (int)wr + 1, nm = (int)wm + 1;
+  const size_t smb = (size_t)(m.nc + m.T) * sizeof(double);
+  int64_t tb = ((int64_t)nr * nm + 127) / 128;
+  if (tb > 148 * 16) tb = 148 * 16;
+  mufreq_table_kernel<<<(unsigned)tb, 128, smb, st>>>(nr, nm, wr, wm, cellularity, ploidy, adr,
+                                                     m, (double4*)table);
+  SQZ_CUDA(cudaGetLastError());
+  int64_t blocks = (N + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  mufreq_lookup_kernel<<<(unsigned)blocks, 256, smb, st>>>(N, d_F, d_ratio, nr, nm, wr, wm,
+                                                          cellularity, ploidy, adr, m,
+                                                          (const double4*)table, d_out);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
 }  // namespace sqz

@@ -69,3 +69,29 @@ def test_mufreq_grid_matches_oracle(oracle):
     b = oracle.finish_model_fit(ref, pl, ce)
     big = b["lpp"] > 1e-290
     np.testing.assert_allclose(a["lpp"][big], b["lpp"][big], rtol=RTOL)
+
+
+def test_mufreq_scalar_table_path_equals_vector_path(oracle):
+    """Scalar weights take the table-driven kernel (sqz_mufreq_point_scalar); the same call
+    with the weights spelled out as vectors takes the direct kernel.  Both must give the
+    oracle's rows, including positions that fall outside the table (NA, ratio < 0, F > 1)."""
+    mut = synth_mutations(30000, seed=17)
+    f, r = mut["mufreq"].copy(), mut["depth_ratio"].copy()
+    f[:6] = [np.nan, 0.0, 1.0, 1.2, -0.1, 0.5]
+    r[:6] = [1.0, np.nan, -0.5, 1.0, 1.0, 1e300]
+    for wm, wr, cn_max in ((100, 100, 7), (100, 100, 20), (37, 250, 7), (1, 1, 7)):
+        a = S.mufreq_bayes(f, r, 0.7, 2.4, 1.0, wm, wr, CNt_max=cn_max, priors_table=PRI)
+        b = S.mufreq_bayes(f, r, 0.7, 2.4, 1.0, np.full(f.size, float(wm)),
+                           np.full(f.size, float(wr)), CNt_max=cn_max, priors_table=PRI)
+        c = oracle.mufreq_bayes(f, r, 0.7, 2.4, 1.0, wm, wr, CNt_max=cn_max, priors_table=PRI)
+        for col in range(4):
+            assert same(a[:, col], b[:, col]), (wm, wr, col)
+        for col in range(3):
+            assert same(a[:, col], c[:, col]), (wm, wr, col)
+        ok = (a[:, 3] == c[:, 3]) | (np.isnan(a[:, 3]) & np.isnan(c[:, 3])) | \
+             (np.abs(a[:, 3] - c[:, 3]) <= RTOL * np.abs(c[:, 3]))
+        assert ok.all()
+    # non-integer scalar weight: no table, direct path, dbinom gives NaN as in R
+    a = S.mufreq_bayes(f[6:50], r[6:50], 0.7, 2.4, 1.0, 10.5, 100)
+    c = oracle.mufreq_bayes(f[6:50], r[6:50], 0.7, 2.4, 1.0, 10.5, 100)
+    assert same(a[:, 1], c[:, 1]) and same(a[:, 3], c[:, 3])
