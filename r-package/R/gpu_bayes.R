@@ -65,9 +65,23 @@ mufreq.bayes <- function(mufreq, depth.ratio, cellularity,
     ploidy, avg.depth.ratio, weight.mufreq = 100, weight.ratio = 100,
     CNt.min = 1, CNt.max = 7, CNn = 2,
     priors.table = data.frame(CN = CNt.min:CNt.max, value = 1)) {
+    p <- .sqz.priors(priors.table)
+    if (length(weight.mufreq) == 1 && length(weight.ratio) == 1 &&
+        weight.mufreq == round(weight.mufreq) && weight.ratio == round(weight.ratio) &&
+        weight.mufreq >= 0 && weight.ratio >= 0 && weight.mufreq <= 4096 &&
+        weight.ratio <= 4096) {
+        # scalar weights (the defaults; R/results.R:153-157): table-driven kernel
+        mufreq.tab <- data.frame(F = mufreq, ratio = depth.ratio)
+        types.L <- .Call(sqzr_mufreq_point_scalar, as.double(mufreq.tab$F),
+            as.double(mufreq.tab$ratio), as.double(weight.mufreq),
+            as.double(weight.ratio), as.double(cellularity), as.double(ploidy),
+            as.double(avg.depth.ratio), as.integer(CNt.min), as.integer(CNt.max),
+            as.integer(CNn), p$CN, p$value)
+        colnames(types.L) <- c("CNn", "CNt", "Mt", "LPP")
+        return(types.L)
+    }
     mufreq.tab <- data.frame(F = mufreq, ratio = depth.ratio,
         weight.mufreq = weight.mufreq, weight.ratio = weight.ratio)
-    p <- .sqz.priors(priors.table)
     types.L <- .Call(sqzr_mufreq_point, as.double(mufreq.tab$F),
         as.double(mufreq.tab$ratio), as.double(mufreq.tab$weight.mufreq),
         as.double(mufreq.tab$weight.ratio), as.double(cellularity), as.double(ploidy),

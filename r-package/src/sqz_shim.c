@@ -101,6 +101,26 @@ SEXP sqzr_mufreq_point(SEXP F, SEXP ratio, SEXP wm, SEXP wr, SEXP cellularity, S
   return out;
 }
 
+/* mufreq.bayes with scalar weights (the reference's defaults, R/results.R:153-157) */
+SEXP sqzr_mufreq_point_scalar(SEXP F, SEXP ratio, SEXP wm, SEXP wr, SEXP cellularity,
+                              SEXP ploidy, SEXP adr, SEXP cn_min, SEXP cn_max, SEXP cnn,
+                              SEXP pCN, SEXP pval) {
+  R_xlen_t n = XLENGTH(F);
+  need_real(F, n, "mufreq");
+  need_real(ratio, n, "depth.ratio");
+  need_real(pCN, -1, "priors.table$CN");
+  need_real(pval, XLENGTH(pCN), "priors.table$value");
+  SEXP out = PROTECT(Rf_allocMatrix(REALSXP, (int)n, 4));
+  int rc = sqz_mufreq_point_scalar(REAL(F), REAL(ratio), (int64_t)n, Rf_asReal(wm),
+                                   Rf_asReal(wr), Rf_asReal(cellularity), Rf_asReal(ploidy),
+                                   Rf_asReal(adr), Rf_asInteger(cn_min), Rf_asInteger(cn_max),
+                                   Rf_asInteger(cnn), REAL(pCN), REAL(pval),
+                                   (int)XLENGTH(pCN), REAL(out));
+  UNPROTECT(1);
+  raise(rc);
+  return out;
+}
+
 /* replaces fit.cp + pblapply in mufreq.model.fit (R/bayes.R:179-185) */
 SEXP sqzr_mufreq_grid(SEXP F, SEXP ratio, SEXP wm, SEXP wr, SEXP ploidy, SEXP cellularity,
                       SEXP adr, SEXP cn_min, SEXP cn_max, SEXP cnn, SEXP pCN, SEXP pval,
@@ -137,6 +157,7 @@ static const R_CallMethodDef call_methods[] = {
     {"sqzr_baf_grid", (DL_FUNC)&sqzr_baf_grid, 17},
     {"sqzr_baf_point", (DL_FUNC)&sqzr_baf_point, 15},
     {"sqzr_mufreq_point", (DL_FUNC)&sqzr_mufreq_point, 12},
+    {"sqzr_mufreq_point_scalar", (DL_FUNC)&sqzr_mufreq_point_scalar, 12},
     {"sqzr_mufreq_grid", (DL_FUNC)&sqzr_mufreq_grid, 13},
     {"sqzr_device_count", (DL_FUNC)&sqzr_device_count, 0},
     {"sqzr_release", (DL_FUNC)&sqzr_release, 0},

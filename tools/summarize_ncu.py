@@ -9,8 +9,9 @@ import json
 import subprocess
 import sys
 
-tag, launches, rep = sys.argv[1], sys.argv[2], sys.argv[3]
-bench = sys.argv[4:]
+tag, launches = sys.argv[1], sys.argv[2]
+reps = [a for a in sys.argv[3:] if a.endswith(".ncu-rep")]
+bench = [a for a in sys.argv[3:] if not a.endswith(".ncu-rep")]
 out = []
 rows = [r for r in csv.reader(open(launches)) if len(r) > 5]
 hdr = rows[0]
@@ -37,40 +38,42 @@ out.append("\nShare of the fit step (the four `baf_*` kernels only):\n")
 for k in step:
     out.append("- `%s`: %.2f%%" % (k, 100 * sum(agg[k]["ns"]) / stot))
 
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True,
-                     text=True).stdout
-r = list(csv.reader(raw.splitlines()))
-h, u, v = r[0], r[1], r[2]
-want = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size",
-        "launch__registers_per_thread", "launch__occupancy_limit_registers",
-        "sm__cycles_elapsed.avg.per_second", "sm__cycles_active.avg", "sm__cycles_elapsed.avg",
-        "sm__throughput.avg.pct_of_peak_sustained_elapsed",
-        "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
-        "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_elapsed",
-        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
-        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
-        "smsp__issue_active.avg.pct_of_peak_sustained_active",
-        "smsp__inst_executed.sum", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "dram__bytes_read.sum", "dram__bytes_write.sum",
-        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-        "smsp__sass_thread_inst_executed_op_dfma_pred_on.sum",
-        "smsp__sass_thread_inst_executed_op_dmul_pred_on.sum",
-        "smsp__sass_thread_inst_executed_op_dadd_pred_on.sum",
-        "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"]
-out.append("\n# ncu --set full, top kernel (%s)\n" % tag)
-out.append("Command: `ncu --set full --clock-control none --import-source on -k "
-           "regex:baf_grid_fast -s 3 -c 1 python bench.py --steps 20 --warmup 3`\n")
-out.append("| metric | unit | value |")
-out.append("|---|---|---|")
-for name in want:
-    for hh, uu, vv in zip(h, u, v):
-        if hh == name:
-            out.append("| %s | %s | %s |" % (hh, uu, vv))
+for rep_ in reps:
+    raw = subprocess.run(["ncu", "-i", rep_, "--page", "raw", "--csv"], capture_output=True,
+                         text=True).stdout
+    r = list(csv.reader(raw.splitlines()))
+    h, u, v = r[0], r[1], r[2]
+    want = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size",
+            "launch__registers_per_thread", "launch__occupancy_limit_registers",
+            "sm__cycles_elapsed.avg.per_second", "sm__cycles_active.avg", "sm__cycles_elapsed.avg",
+            "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+            "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+            "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_elapsed",
+            "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+            "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+            "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+            "smsp__issue_active.avg.pct_of_peak_sustained_active",
+            "smsp__inst_executed.sum", "sm__warps_active.avg.pct_of_peak_sustained_active",
+            "dram__bytes_read.sum", "dram__bytes_write.sum",
+            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+            "smsp__sass_thread_inst_executed_op_dfma_pred_on.sum",
+            "smsp__sass_thread_inst_executed_op_dmul_pred_on.sum",
+            "smsp__sass_thread_inst_executed_op_dadd_pred_on.sum",
+            "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"]
+    out.append("\n# ncu --set full (%s): %s\n" % (tag, rep_.split("/")[-1]))
+    out.append("Command: `ncu --set full --clock-control none --import-source on -k "
+               "regex:<kernel> -s 3 -c 1 python bench.py [--workload config3] ...` (after the "
+               "same command exited 0 without ncu)\n")
+    out.append("| metric | unit | value |")
+    out.append("|---|---|---|")
+    for name in want:
+        for hh, uu, vv in zip(h, u, v):
+            if hh == name:
+                out.append("| %s | %s | %s |" % (hh, uu, vv))
 for b in bench:
     for line in open(b):
         if line.startswith("{"):
