@@ -31,7 +31,9 @@ __global__ void __launch_bounds__(256)
 baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
                    double2* __restrict__ cw) {
   extern __shared__ __align__(16) double sm[];
-  double* mb = sm;  // [T] model BAF of this column (R/model.R:9-14)
+  double* mb = sm;            // [T] model BAF of this column (R/model.R:9-14)
+  double* b_a = sm + m.T;     // [nc] model BAF at B = 0
+  double* b_invd = b_a + m.nc;  // [nc] 1 / (model BAF step per unit of B)
   const double cell = a.cell[ic0 + blockIdx.y];
   for (int t = threadIdx.x; t < m.T; t += blockDim.x) {
     int c = 0;
@@ -39,33 +41,38 @@ baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
     mb[t] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
                             (double)m.CNn);
   }
+  for (int c = threadIdx.x; c < m.nc; c += blockDim.x) {
+    const double den = ((double)(m.CNt_min + c) * cell) + (double)m.CNn * (1 - cell);
+    b_a[c] = (1 - cell) / den;
+    b_invd[c] = den / cell;
+  }
   __syncthreads();
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= N_total) return;
   const double2 bk = a.bk[s];
+  const double Bf = a.Bf[s];
   double2* out = cw + (int64_t)blockIdx.y * m.nc * N_total + s;
-  int t = 0;
   for (int c = 0; c < m.nc; ++c) {
-    // min over B of |xb|: NaN never wins (R/bayes.R:70-72, which.max skips NaN); four
-    // independent running minima, |.| folded into the compare
-    const int tend = m.toff[c + 1];
-    double m0 = INF, m1 = INF, m2 = INF, m3 = INF;
-    for (; t + 4 <= tend; t += 4) {
-      const double x0 = fma(mb[t], bk.x, bk.y), x1 = fma(mb[t + 1], bk.x, bk.y);
-      const double x2 = fma(mb[t + 2], bk.x, bk.y), x3 = fma(mb[t + 3], bk.x, bk.y);
+    // min over B of |xb| with xb = (mb_B - Bf) kb: NaN never wins (R/bayes.R:70-72,
+    // which.max skips NaN).  The model BAF is linear in B (R/model.R:10-11), so for a
+    // copy number with many rows only the two rows that bracket Bf are read: the nearest
+    // row is always one of them (also when rounding puts floor() one off, because then Bf
+    // sits on a row and that row is in both brackets).  Short rows are scanned.
+    const int t0 = m.toff[c], nb = m.toff[c + 1] - t0;
+    double m0 = INF;
+    if (nb > 3) {
+      int b0 = __double2int_rd((Bf - b_a[c]) * b_invd[c]);  // NaN -> 0
+      b0 = max(0, min(b0, nb - 2));
+      const double x0 = fma(mb[t0 + b0], bk.x, bk.y), x1 = fma(mb[t0 + b0 + 1], bk.x, bk.y);
       if (fabs(x0) < fabs(m0)) m0 = x0;
-      if (fabs(x1) < fabs(m1)) m1 = x1;
-      if (fabs(x2) < fabs(m2)) m2 = x2;
-      if (fabs(x3) < fabs(m3)) m3 = x3;
+      if (fabs(x1) < fabs(m0)) m0 = x1;
+    } else {
+      for (int t = t0; t < t0 + nb; ++t) {
+        const double x0 = fma(mb[t], bk.x, bk.y);
+        if (fabs(x0) < fabs(m0)) m0 = x0;
+      }
     }
-    for (; t < tend; ++t) {
-      const double x0 = fma(mb[t], bk.x, bk.y);
-      if (fabs(x0) < fabs(m0)) m0 = x0;
-    }
-    if (fabs(m1) < fabs(m0)) m0 = m1;
-    if (fabs(m3) < fabs(m2)) m2 = m3;
-    if (fabs(m2) < fabs(m0)) m0 = m2;
     const double u = fma(m0, m0, 1.0);  // 1 + xb^2/5
     if (a.rp) {
       out[(int64_t)c * N_total] = make_double2(u, 0.0);
@@ -518,8 +525,8 @@ int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, i
   for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += nCb_max) {
     const int nCb = (int)((a.nCs - ic0 < nCb_max) ? (a.nCs - ic0) : nCb_max);
     dim3 grid((unsigned)((N_total + 255) / 256), (unsigned)nCb);
-    baf_colterm_kernel<<<grid, 256, (size_t)m.T * sizeof(double), st>>>(a, m, (int)ic0, N_total,
-                                                                        cw);
+    baf_colterm_kernel<<<grid, 256, (size_t)(m.T + 2 * m.nc) * sizeof(double), st>>>(
+        a, m, (int)ic0, N_total, cw);
     SQZ_CUDA(cudaGetLastError());
     int rc;
     if (prune) {
