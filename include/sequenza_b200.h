@@ -223,6 +223,31 @@ int sqz_mufreq_grid_dev(const double* d_mufreq, const double* d_depth_ratio,
 size_t sqz_mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nC_shard);
 
 /* ---------------------------------------------------------------------------------
+ * After the grid: normalisation (R/bayes.R:120-122) and the reductions get.ci needs
+ * (R/solutions.R:1-15), for S result$LPP vectors of one nP x nC grid (S > 1: a cohort).
+ *   lpp            S x (nP*nC): exp(LPP - LogSumLik); as an R matrix [ploidy x cellularity]
+ *                  (column-major) when the grid axes are already sorted and unique
+ *   row_max        S x nP: apply(lpp, 1, max)        col_max        S x nC: apply(lpp, 2, max)
+ *   row_mass_above S x nP, col_mass_above S x nC: total lpp mass of the grid points whose
+ *                  lpp is strictly greater than that marginal maximum.  A marginal value is
+ *                  inside get.ci's `level` region iff its mass_above < level -- the same
+ *                  set the reference gets from sort + cumsum (R/solutions.R:2-5, :10-14),
+ *                  without a sort.  Masses are accumulated in 2^-62 fixed point.
+ *   log_sum_lik    S: LogSumLik
+ * max(na.rm = TRUE) / sum() without na.rm as in the reference (any NaN in LPP makes the
+ * whole lpp NaN).  Requires nP + nC <= 4096.  The tapply step (R/bayes.R:117) is the
+ * identity for sorted unique axes; callers with duplicated or unsorted axis values keep
+ * the R code.
+ * --------------------------------------------------------------------------------- */
+int sqz_fit_finish(const double* lpp_sum, int64_t S, int64_t nP, int64_t nC, double* lpp,
+                   double* row_max, double* col_max, double* row_mass_above,
+                   double* col_mass_above, double* log_sum_lik);
+int sqz_fit_finish_dev(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t nC,
+                       double* d_lpp, double* d_row_max, double* d_col_max,
+                       double* d_row_mass_above, double* d_col_mass_above,
+                       double* d_log_sum_lik, void* stream);
+
+/* ---------------------------------------------------------------------------------
  * Model points as the kernels compute them (R/model.R:49-67), for checking the device
  * arithmetic against tests/testthat/test.model.R.  out is T x 5 column-major:
  * CNt, second index (B or Mt), model depth.ratio, model BAF or mufreq, normalised prior.

@@ -40,14 +40,56 @@ def _r_label(x):
     return float("%.15g" % x)
 
 
-def finish_model_fit(lpp_sum, ploidy, cellularity):
+class CpTable(dict):
+    """list(ploidy, cellularity, lpp) as a dict.  When the device produced it
+    (sqz_fit_finish) it also carries, outside the mapping, the reductions get.ci needs, so
+    that get_ci() does not have to sort the matrix again."""
+    ci_cache = None
+
+
+def finish_model_fit_device(lpp_sum, x, y):
+    """R/bayes.R:120-122 and the get.ci reductions on the GPU (sqz_fit_finish) for sorted,
+    unique axis values x (ploidy) and y (cellularity); lpp_sum may hold several samples."""
+    nP, nC = x.size, y.size
+    lpp_sum = np.ascontiguousarray(lpp_sum, dtype=np.float64).reshape(-1, nP * nC)
+    S = lpp_sum.shape[0]
+    lpp = np.empty((S, nP * nC))
+    rmax, rab = np.empty((S, nP)), np.empty((S, nP))
+    cmax, cab = np.empty((S, nC)), np.empty((S, nC))
+    lsl = np.empty(S)
+    _lib.check(_lib.lib().sqz_fit_finish(
+        _lib.ptr(lpp_sum), S, nP, nC, _lib.ptr(lpp), _lib.ptr(rmax), _lib.ptr(cmax),
+        _lib.ptr(rab), _lib.ptr(cab), _lib.ptr(lsl)))
+    out = []
+    for k in range(S):
+        t = CpTable(ploidy=x.copy(), cellularity=y.copy(),
+                    lpp=lpp[k].reshape(nC, nP).T)  # R matrix [ploidy x cellularity]
+        t.ci_cache = {"lpp_id": id(t["lpp"]), "row_max": rmax[k], "col_max": cmax[k],
+                      "row_above": rab[k], "col_above": cab[k], "log_sum_lik": lsl[k]}
+        out.append(t)
+    return out
+
+
+def finish_model_fit(lpp_sum, ploidy, cellularity, device=None):
     """R/bayes.R:116-123 on the length-G vector the GPU returned: tapply(mean) into a
     [ploidy x cellularity] matrix whose axes went through character dimnames, then
-    LogSumLik (max with na.rm, sum without) and exp(z - LogSumLik)."""
+    LogSumLik (max with na.rm, sum without) and exp(z - LogSumLik).
+    device=None: use the GPU (sqz_fit_finish) when the axes are sorted and unique, there is
+    no NaN and a device is present; False: numpy (the reference's steps, one by one)."""
     pl, ce = _lib.vec(ploidy), _lib.vec(cellularity)
     lpp_sum = _lib.vec(lpp_sum, pl.size * ce.size, "lpp_sum")
     x, pi = np.unique(np.array([_r_label(v) for v in pl]), return_inverse=True)
     y, ci = np.unique(np.array([_r_label(v) for v in ce]), return_inverse=True)
+    if device is None or device:
+        sorted_unique = (x.size == pl.size and y.size == ce.size and
+                         np.array_equal(pi, np.arange(pl.size)) and
+                         np.array_equal(ci, np.arange(ce.size)))
+        usable = (sorted_unique and pl.size + ce.size <= 4096 and pl.size * ce.size > 0 and
+                  not np.isnan(lpp_sum).any())
+        if usable and (device or _lib.lib().sqz_device_count() > 0):
+            return finish_model_fit_device(lpp_sum, x, y)[0]
+        if device:
+            raise ValueError("device finish needs sorted unique axes, no NaN, <= 4096 values")
     grid = lpp_sum.reshape(ce.size, pl.size)  # expand.grid: ploidy varies fastest
     if x.size == pl.size and y.size == ce.size:
         z = np.empty((x.size, y.size))
@@ -133,6 +175,11 @@ def baf_model_fit_batch(samples, cellularity=None, ploidy=None, n_gpus=None, CNt
         _lib.ptr(ce), ce.size, _lib.ptr(adr), int(CNt_min), int(CNt_max), int(CNn),
         _lib.ptr(pc), _lib.ptr(pv), pc.size, int(bool(ratio_priority)), int(n_gpus),
         int(mode), _lib.ptr(out)))
+    x = np.array([_r_label(v) for v in pl])
+    y = np.array([_r_label(v) for v in ce])
+    if (S > 0 and np.all(np.diff(x) > 0) and np.all(np.diff(y) > 0) and
+            pl.size + ce.size <= 4096 and not np.isnan(out).any()):
+        return finish_model_fit_device(out, x, y)  # one launch for the whole cohort
     return [finish_model_fit(out[k * G:(k + 1) * G], pl, ce) for k in range(S)]
 
 

@@ -59,6 +59,10 @@ int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t
                                int CNt_min, int CNt_max, int CNn, const double* prior_CN,
                                const double* prior_value, int n_prior, void* table,
                                size_t table_bytes, cudaStream_t st, double* d_out);
+int fit_finish_launch(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t nC,
+                      double* d_znorm, double* d_row_max, double* d_col_max,
+                      double* d_row_above, double* d_col_above, double* d_lsl,
+                      cudaStream_t st);
 int model_points_launch(int kind, double cellularity, double ploidy, double adr, int CNt_min,
                         int CNt_max, int CNn, const double* prior_CN,
                         const double* prior_value, int n_prior, int* T_out, double* h_out);
@@ -502,6 +506,64 @@ int sqz_mufreq_grid(const double* mufreq, const double* depth_ratio,
     SQZ_CUDA(cudaSetDevice(d));
     SQZ_CUDA(cudaStreamSynchronize(g_ctx[d].st));
   }
+  return SQZ_OK;
+}
+
+int sqz_fit_finish_dev(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t nC,
+                       double* d_lpp, double* d_row_max, double* d_col_max,
+                       double* d_row_mass_above, double* d_col_mass_above,
+                       double* d_log_sum_lik, void* stream) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return fit_finish_launch(d_lpp_sum, S, nP, nC, d_lpp, d_row_max, d_col_max, d_row_mass_above,
+                           d_col_mass_above, d_log_sum_lik, (cudaStream_t)stream);
+}
+
+int sqz_fit_finish(const double* lpp_sum, int64_t S, int64_t nP, int64_t nC, double* lpp,
+                   double* row_max, double* col_max, double* row_mass_above,
+                   double* col_mass_above, double* log_sum_lik) {
+  if (S < 0 || nP < 1 || nC < 1) return fail(SQZ_ERR_ARG, "need S >= 0, nP >= 1, nC >= 1");
+  if (S > 0 && (!lpp_sum || !lpp || !row_max || !col_max || !row_mass_above ||
+                !col_mass_above || !log_sum_lik))
+    return fail(SQZ_ERR_ARG, "null pointer argument");
+  if (S == 0) return SQZ_OK;
+  int ndev = 0;
+  int rc = usable_devices(1, &ndev);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_mu);
+  int cur = 0;
+  SQZ_CUDA(cudaGetDevice(&cur));
+  DevCtx* c;
+  if ((rc = ctx_for(cur, &c))) return rc;
+  const size_t G = (size_t)(nP * nC), nS = (size_t)S;
+  const size_t in_b = a256(nS * G * 8);
+  const size_t out_b = a256(nS * G * 8) + 2 * a256(nS * nP * 8) + 2 * a256(nS * nC * 8) +
+                       a256(nS * 8);
+  if ((rc = grow(&c->in, &c->in_cap, in_b))) return rc;
+  if ((rc = grow(&c->out, &c->out_cap, out_b))) return rc;
+  char* p = (char*)c->out;
+  double* d_zn = (double*)p;
+  p += a256(nS * G * 8);
+  double* d_rm = (double*)p;
+  p += a256(nS * nP * 8);
+  double* d_ra = (double*)p;
+  p += a256(nS * nP * 8);
+  double* d_cm = (double*)p;
+  p += a256(nS * nC * 8);
+  double* d_ca = (double*)p;
+  p += a256(nS * nC * 8);
+  double* d_l = (double*)p;
+  SQZ_CUDA(cudaMemcpyAsync(c->in, lpp_sum, nS * G * 8, cudaMemcpyHostToDevice, c->st));
+  rc = fit_finish_launch((const double*)c->in, S, nP, nC, d_zn, d_rm, d_cm, d_ra, d_ca, d_l,
+                         c->st);
+  if (rc) return rc;
+  SQZ_CUDA(cudaMemcpyAsync(lpp, d_zn, nS * G * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaMemcpyAsync(row_max, d_rm, nS * nP * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaMemcpyAsync(row_mass_above, d_ra, nS * nP * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaMemcpyAsync(col_max, d_cm, nS * nC * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaMemcpyAsync(col_mass_above, d_ca, nS * nC * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaMemcpyAsync(log_sum_lik, d_l, nS * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaStreamSynchronize(c->st));
   return SQZ_OK;
 }
 

@@ -20,6 +20,22 @@ def get_ci(cp_table, level=0.95):
     lpp = np.asarray(cp_table["lpp"], dtype=np.float64)
     ploidy = np.asarray(cp_table["ploidy"], dtype=np.float64)
     cell = np.asarray(cp_table["cellularity"], dtype=np.float64)
+    cache = getattr(cp_table, "ci_cache", None)
+    if cache is not None and cache["lpp_id"] == id(cp_table["lpp"]) and np.ndim(level) == 0:
+        # reductions already made on the device (sqz_fit_finish): a marginal maximum is at
+        # or above the threshold element iff the mass strictly above it is < level
+        vx, vy = cache["row_max"], cache["col_max"]
+        sel_x = ploidy[cache["row_above"] < level]
+        sel_y = cell[cache["col_above"] < level]
+        if sel_x.size and sel_y.size:
+            return {
+                "values.ploidy": {"x": ploidy.copy(), "y": vx / np.sum(vx)},
+                "confint.ploidy": (float(sel_x.min()), float(sel_x.max())),
+                "max.ploidy": float(ploidy[_which_max(vx)]),
+                "values.cellularity": {"x": vy / np.sum(vy), "y": cell.copy()},
+                "confint.cellularity": (float(sel_y.min()), float(sel_y.max())),
+                "max.cellularity": float(cell[_which_max(vy)]),
+            }
     flat = lpp.reshape(-1)
     znormsort = np.sort(flat[~np.isnan(flat)])[::-1]          # sort(decreasing = TRUE)
     cum = np.cumsum(znormsort.astype(np.longdouble)).astype(np.float64)  # long double acc
