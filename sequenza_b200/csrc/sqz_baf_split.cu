@@ -9,9 +9,10 @@
 //                        copy number, stored as (wub, sqrt(wub)) in a column-major scratch
 //                        [column][CNt][segment] (coalesced over segments);
 //   baf_grid_split_kernel one CTA per (sample, cellularity, ploidy tile, segment chunk):
-//                        every thread streams its segments' scratch rows into its own
-//                        shared-memory column with cp.async, double-buffered one segment
-//                        ahead, and evaluates
+//                        the scratch rows of the CTA's next 128 segments are staged in
+//                        shared memory by TMA bulk copies (cp.async.bulk + mbarrier, one
+//                        row per copy number, two stages); every thread reads its own
+//                        16-byte entry of each row and evaluates
 //                            q = (xr' * sqrt(wub))^2 + wub            (2 DFMA)
 //                            qmin = min(qmin, q)                      (DSETP + 2 FSEL)
 //                        for PT ploidies per copy number.  Running products stay in
@@ -95,7 +96,41 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// ---- TMA (bulk async copy) + mbarrier helpers ------------------------------------------
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  const unsigned addr = (unsigned)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(addr), "r"(parity) : "memory");
+}
+// one contiguous row global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gsrc, unsigned bytes,
+                                             unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes),
+      "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+
 // ---- grid kernel ------------------------------------------------------------------------
+// Staging of the pre-pass rows: one elected thread issues a bulk async copy (TMA, 1-D) per
+// copy number for the CTA's next 128 segments -- each row of the scratch is contiguous over
+// segments -- into the other half of a two-stage shared-memory buffer; an mbarrier per
+// stage counts the bytes; every thread then reads its own 16-byte entry of each row.
 template <int PT, bool RP>
 __global__ void __launch_bounds__(128, 2)
 baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
@@ -109,6 +144,7 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   __shared__ double redM[4][PT];
   __shared__ long long redE[4][PT];
   __shared__ unsigned redBad[4];
+  __shared__ __align__(8) unsigned long long bar[2];
 
   int64_t b = blockIdx.x;
   const int pt = (int)(b % a.nPT);
@@ -119,6 +155,11 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   const int64_t smp = b / a.nChunk;
   const int ic = ic0 + icl;
   const int p0 = pt * PT;
+  if (tid == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
 
   // log model depth ratio of this (cellularity, ploidy tile): R/model.R:1-7, :49-56
   const double cell = a.cell[ic];
@@ -145,31 +186,36 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   unsigned bad = 0;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
-  // Each thread copies only its own 16-byte entries and reads only those back, so
-  // cp.async.wait_group is all the synchronisation the staging needs.
-  auto issue = [&](int buf, int64_t seg) {
-    double2* dst = stage + (buf * m.nc) * nthr + tid;
-    const double2* src = cwc + seg;
-    for (int c = 0; c < m.nc; ++c) cp_async16(dst + c * nthr, src + (int64_t)c * N_total);
-    cp_async_commit();
+  const int n_it = ce > cb ? (int)((ce - cb + nthr - 1) / nthr) : 0;
+  auto issue = [&](int buf, int itn) {  // elected thread: rows of the CTA's iteration itn
+    const int64_t base = cb + (int64_t)itn * nthr;
+    const unsigned cnt = (unsigned)min((int64_t)nthr, ce - base);
+    mbar_expect_tx(&bar[buf], (unsigned)m.nc * cnt * (unsigned)sizeof(double2));
+    double2* dst = stage + (buf * m.nc) * nthr;
+    const double2* src = cwc + base;
+    for (int c = 0; c < m.nc; ++c, dst += nthr, src += N_total)
+      tma_bulk_g2s(dst, src, cnt * (unsigned)sizeof(double2), &bar[buf]);
   };
 
   int64_t s = cb + tid;
   double2 rk_n = make_double2(0., 0.);
-  if (s < ce) {
-    rk_n = a.rk[s];
-    issue(0, s);
-  }
-  int it = 0, buf = 0;
-  while (s < ce) {
+  if (s < ce) rk_n = a.rk[s];
+  if (tid == 0 && n_it > 0) issue(0, 0);
+  int it = 0;
+  for (int itn = 0; itn < n_it; ++itn) {
+    const int buf = itn & 1;
+    const bool act = s < ce;
     const double2 rk = rk_n;
     const int64_t sn = s + nthr;
-    if (sn < ce) {  // next segment of this thread: ratio terms to registers, BAF rows to smem
-      rk_n = a.rk[sn];
-      issue(buf ^ 1, sn);
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
+    if (itn + 1 < n_it) {
+      __syncthreads();  // every thread has finished reading the other stage (iteration itn-1)
+      if (tid == 0) issue(buf ^ 1, itn + 1);
+      if (sn < ce) rk_n = a.rk[sn];  // ratio terms of the next segment: register prefetch
+    }
+    mbar_wait(&bar[buf], (unsigned)((itn >> 1) & 1));
+    if (!act) {
+      s = sn;
+      continue;
     }
     const double2* col = stage + (buf * m.nc) * nthr + tid;
 
@@ -221,7 +267,6 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
       }
     }
     s = sn;
-    buf ^= 1;
   }
 
   // CTA reduction: sum of log(mantissa) (each in [0, log 2)), exact integer exponents
