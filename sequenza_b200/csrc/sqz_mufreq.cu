@@ -278,28 +278,70 @@ int model_points_launch(int kind, double cellularity, double ploidy, double adr,
 // (R/results.R:153-157).  Then the row of a position is a function of
 //   k_r = round(w.r * r/(1+r)) in 0..w.r   and   k_m = round(F * w.m) in 0..w.m
 // alone, so the (w.r+1) x (w.m+1) answers are computed once with the same nmath sequence
-// (mufreq_table_kernel, one thread per pair) and the per-position kernel becomes a
+// (mufreq_scores_kernel: one thread per binomial density; mufreq_table_kernel: one thread
+// per pair of counts) and the per-position kernel becomes a
 // streaming lookup: 16 bytes in, 32 bytes out, HBM-bound.  Positions whose counts fall
 // outside the table (NA, negative ratio, F outside [0,1]) take the direct path.
+// Stage 1: every binomial density the table needs, one thread each:
+//   srp[kr][c] = dbinom(kr, w.r, prob_c) * prior_c     (score.r, R/bayes.R:149-153)
+//   smv[km][t] = dbinom(km, w.m, mufreq_t)             (score.m, R/bayes.R:151-152)
 __global__ void __launch_bounds__(128)
-mufreq_table_kernel(int nr, int nm, double wr, double wm, double cell, double ploidy,
-                    double adr, CnModel m, double4* __restrict__ table) {
+mufreq_scores_kernel(int nr, int nm, double wr, double wm, double cell, double ploidy,
+                     double adr, CnModel m, double* __restrict__ srp, double* __restrict__ smv) {
   extern __shared__ double sm[];
   double* probr = sm;
   double* mm = sm + m.nc;
   build_muf_model(m, cell, ploidy, adr, probr, mm);
   __syncthreads();
+  const int64_t n1 = (int64_t)nr * m.nc, n = n1 + (int64_t)nm * m.T;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    if (i < n1) {
+      const int kr = (int)(i / m.nc), c = (int)(i - (int64_t)kr * m.nc);
+      srp[i] = binom_finish(binom_hoist((double)kr, wr), probr[c]) * m.prior[c];
+    } else {
+      const int64_t k = i - n1;
+      const int km = (int)(k / m.T), t = (int)(k - (int64_t)km * m.T);
+      smv[k] = binom_finish(binom_hoist((double)km, wm), mm[t]);
+    }
+  }
+}
+
+// Stage 2: which.max(score.r) per kr (first maximum, NaN skipped), then for every (kr, km)
+// the first maximum of log(post) among the rows of that copy number (R/bayes.R:155-164).
+__global__ void __launch_bounds__(128)
+mufreq_table_kernel(int nr, int nm, CnModel m, const double* __restrict__ srp,
+                    const double* __restrict__ smv, double4* __restrict__ table) {
   const int64_t n = (int64_t)nr * nm;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int kr = (int)(i / nm), km = (int)(i - (int64_t)kr * nm);
-    const BinomHoist hr = binom_hoist((double)kr, wr), hm = binom_hoist((double)km, wm);
-    int kc, kt;
-    double lpp;
-    mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
-    table[i] = make_double4(kc >= 0 ? (double)m.CNn : na_real(),
-                            kc >= 0 ? (double)(m.CNt_min + kc) : na_real(),
-                            kc >= 0 ? (double)kt : na_real(), lpp);
+    int kc = -1;
+    double bests = 0.;
+    for (int c = 0; c < m.nc; ++c) {
+      const double sr = srp[(int64_t)kr * m.nc + c];
+      if (!isnan(sr) && (kc < 0 || sr > bests)) {
+        bests = sr;
+        kc = c;
+      }
+    }
+    int k = -1;
+    double best = 0.;
+    if (kc >= 0)
+      for (int t = m.toff[kc]; t < m.toff[kc + 1]; ++t) {
+        double post = bests * smv[(int64_t)km * m.T + t];
+        if (post == 0) post = __longlong_as_double(2LL);  // 1e-323
+        const double lp = log(post);
+        if (!isnan(lp) && (k < 0 || lp > best)) {
+          best = lp;
+          k = t;
+        }
+      }
+    const bool ok = kc >= 0 && k >= 0;
+    table[i] = make_double4(ok ? (double)m.CNn : na_real(),
+                            ok ? (double)(m.CNt_min + kc) : na_real(),
+                            ok ? (double)(k - m.toff[kc]) : na_real(),
+                            ok ? best : __longlong_as_double(0x7FF8000000000000LL));
   }
 }
 
@@ -360,7 +402,10 @@ mufreq_lookup_kernel(int64_t N, const double* __restrict__ F, const double* __re
 size_t mufreq_scalar_table_bytes(double wm, double wr) {
   if (!(wm >= 0) || !(wr >= 0) || wm != nearbyint(wm) || wr != nearbyint(wr)) return 0;
   if (wm > 4096 || wr > 4096 || (wm + 1) * (wr + 1) > 4.0e6) return 0;
-  return (size_t)((wm + 1) * (wr + 1)) * sizeof(double4);
+  // answer table + the two score tables of stage 1, sized for any copy-number range
+  return (size_t)((wm + 1) * (wr + 1)) * sizeof(double4) +
+         (size_t)(wr + 1) * kMaxCN * sizeof(double) +
+         (size_t)(wm + 1) * kMaxTypes * sizeof(double);
 }
 
 int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t N, double wm,
@@ -382,10 +427,16 @@ int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t
   if (N == 0) return SQZ_OK;
   const int nr = (int)wr + 1, nm = (int)wm + 1;
   const size_t smb = (size_t)(m.nc + m.T) * sizeof(double);
+  double* srp = (double*)((char*)table + (size_t)nr * nm * sizeof(double4));
+  double* smv = srp + (size_t)nr * kMaxCN;
+  int64_t sb = ((int64_t)nr * m.nc + (int64_t)nm * m.T + 127) / 128;
+  if (sb > 148 * 16) sb = 148 * 16;
+  mufreq_scores_kernel<<<(unsigned)sb, 128, smb, st>>>(nr, nm, wr, wm, cellularity, ploidy, adr,
+                                                      m, srp, smv);
+  SQZ_CUDA(cudaGetLastError());
   int64_t tb = ((int64_t)nr * nm + 127) / 128;
   if (tb > 148 * 16) tb = 148 * 16;
-  mufreq_table_kernel<<<(unsigned)tb, 128, smb, st>>>(nr, nm, wr, wm, cellularity, ploidy, adr,
-                                                     m, (double4*)table);
+  mufreq_table_kernel<<<(unsigned)tb, 128, 0, st>>>(nr, nm, m, srp, smv, (double4*)table);
   SQZ_CUDA(cudaGetLastError());
   int64_t blocks = (N + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
