@@ -318,12 +318,16 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
 // q_cj >= LB_c >= qmin_j for every j, so it cannot lower any minimum: the result equals
 // evaluating all of them.  Candidates differ per thread; the rows of the model table are
 // padded by two doubles so that threads reading different rows hit different banks.
-template <int PT>
+// NCT > 0: the number of copy numbers is a compile-time constant (8 = sequenza.fit's CNt
+// 0..7), which lets the bound pass unroll into independent chains held in registers.
+template <int PT, int NCT>
 __global__ void __launch_bounds__(128, 2)
 baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
                        int nCb, int64_t N_total, double* __restrict__ partM,
                        long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int LS = PT + 2;  // padded row stride of the log-ratio table
+  constexpr bool FIX = NCT > 0;
+  const int nc = FIX ? NCT : m.nc;
   extern __shared__ __align__(16) double sm[];
   const int nthr = blockDim.x, tid = threadIdx.x;
   double* lmr = sm;                                                  // [nc][LS]
@@ -381,7 +385,8 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   auto issue = [&](int buf, int64_t seg) {
     double2* dst = stage + (buf * m.nc) * nthr + tid;
     const double2* src = cwc + seg;
-    for (int c = 0; c < m.nc; ++c, dst += nthr, src += N_total) cp_async16(dst, src);
+#pragma unroll
+    for (int c = 0; c < nc; ++c, dst += nthr, src += N_total) cp_async16(dst, src);
     cp_async_commit();
   };
 
@@ -408,15 +413,18 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     // high words with the copy-number index packed into the low six bits
     const double akr = fabs(rk.x);
     unsigned kbest = 0xFFFFFFFFu;
-    for (int c = 0; c < m.nc; ++c) {
+    double lbr[FIX ? NCT : 1];
+#pragma unroll
+    for (int c = 0; c < nc; ++c) {
       double t = fabs(fma(lmid[c], rk.x, rk.y)) - lhw[c] * akr;
       if (t < 0.0) t = 0.0;
       const double wv = col[c * nthr].x;
       const double lb = fma(wv, t * t, wv);
-      LBc[c * nthr + tid] = lb;
+      if (FIX) lbr[FIX ? c : 0] = lb;
+      else LBc[c * nthr + tid] = lb;
       kbest = min(kbest, ((unsigned)__double2hiint(lb) & 0xFFFFFFC0u) | (unsigned)c);
     }
-    const int first = (int)(kbest & 63u) < m.nc ? (int)(kbest & 63u) : 0;
+    const int first = (int)(kbest & 63u) < nc ? (int)(kbest & 63u) : 0;
 
     double qmin[PT];
 #pragma unroll
@@ -440,8 +448,9 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     const double qmax = qh >= 0x7FF00000u ? INF : __hiloint2double((int)(qh + 1u), 0);
     // (d) the copy numbers that can still lower a minimum
     unsigned long long need = 0;
-    for (int c = 0; c < m.nc; ++c)
-      if (LBc[c * nthr + tid] < qmax) need |= 1ull << c;
+#pragma unroll
+    for (int c = 0; c < nc; ++c)
+      if ((FIX ? lbr[FIX ? c : 0] : LBc[c * nthr + tid]) < qmax) need |= 1ull << c;
     need &= ~(1ull << first);
     n_eval += 1u + (unsigned)__popcll(need);
     while (need) {  // per-thread trip count; the warp runs as long as its slowest lane
@@ -526,12 +535,20 @@ static int launch_pruned(const BafGridArgs& a, const CnModel& m, int threads, in
                          const double2* cw, int ic0, int nCb, double* partM, long long* partE,
                          unsigned long long* stats, cudaStream_t st) {
   const size_t smb = pruned_smem_bytes(m.nc, PT, threads);
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  baf_grid_pruned_kernel<PT><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb, N_total,
-                                                                  partM, partE, stats);
+  if (m.nc == 8) {  // CNt 0..7, what sequenza.fit always uses (R/bayes.R:40)
+    SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT, 8>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    baf_grid_pruned_kernel<PT, 8><<<(unsigned)ctas, threads, smb, st>>>(
+        a, m, cw, ic0, nCb, N_total, partM, partE, stats);
+    SQZ_CUDA(cudaGetLastError());
+    return SQZ_OK;
+  }
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT, 0>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  baf_grid_pruned_kernel<PT, 0><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb, N_total,
+                                                                     partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
