@@ -131,11 +131,12 @@ __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gsrc, u
 // copy number for the CTA's next 128 segments -- each row of the scratch is contiguous over
 // segments -- into the other half of a two-stage shared-memory buffer; an mbarrier per
 // stage counts the bytes; every thread then reads its own 16-byte entry of each row.
-template <int PT, bool RP>
+template <int PT, bool RP, int NCT>
 __global__ void __launch_bounds__(128, 2)
 baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
                       int nCb, int64_t N_total, double* __restrict__ partM,
                       long long* __restrict__ partE) {
+  const int nc = NCT > 0 ? NCT : m.nc;  // compile-time for the two usual ranges (0..7, 0..20)
   extern __shared__ __align__(16) double sm[];
   const int nthr = blockDim.x, tid = threadIdx.x;
   double* lmr = sm;                                                // [nc][PT]
@@ -193,7 +194,7 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
     mbar_expect_tx(&bar[buf], (unsigned)m.nc * cnt * (unsigned)sizeof(double2));
     double2* dst = stage + (buf * m.nc) * nthr;
     const double2* src = cwc + base;
-    for (int c = 0; c < m.nc; ++c, dst += nthr, src += N_total)
+    for (int c = 0; c < nc; ++c, dst += nthr, src += N_total)
       tma_bulk_g2s(dst, src, cnt * (unsigned)sizeof(double2), &bar[buf]);
   };
 
@@ -228,7 +229,7 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
       for (int j = 0; j < (RP ? PT : 1); ++j) sel[j] = 1.0;
     }
 #pragma unroll 2
-    for (int c = 0; c < m.nc; ++c) {
+    for (int c = 0; c < nc; ++c) {
       const double2 cwv = col[c * nthr];
       const double* l = lmr + c * PT;
       if (!RP) {
@@ -562,12 +563,19 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
                         const double2* cw, int ic0, int nCb, double* partM, long long* partE,
                         cudaStream_t st) {
   const size_t smb = split_smem_bytes(m.nc, PT, threads);
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_split_kernel<PT, RP>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  baf_grid_split_kernel<PT, RP><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb,
-                                                                      N_total, partM, partE);
+#define SQZ_SPLIT_NC(NCV)                                                                   \
+  do {                                                                                      \
+    SQZ_CUDA(cudaFuncSetAttribute(baf_grid_split_kernel<PT, RP, NCV>,                       \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+    baf_grid_split_kernel<PT, RP, NCV><<<(unsigned)ctas, threads, smb, st>>>(               \
+        a, m, cw, ic0, nCb, N_total, partM, partE);                                         \
+  } while (0)
+  if (!RP && m.nc == 21) SQZ_SPLIT_NC(21);
+  else if (!RP && m.nc == 8) SQZ_SPLIT_NC(8);
+  else SQZ_SPLIT_NC(0);
+#undef SQZ_SPLIT_NC
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
