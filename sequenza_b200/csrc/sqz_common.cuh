@@ -15,7 +15,6 @@
 namespace sqz {
 
 // ---- error plumbing (host) ------------------------------------------------------
-void set_error(const std::string& msg);
 int fail(int code, const std::string& msg);
 
 #define SQZ_CUDA(call)                                                              \
