@@ -133,6 +133,16 @@ class ClockSampler:
         return out
 
 
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from
+    the committed ncu --set full capture of this workload (profiles/r01_traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            return json.load(f)[workload]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def cpu_baseline(w, steps=1, warmup=0):
     """The oracle (CPU restatement, all host threads) on a bounded contiguous block of
     this workload's grid points.  Returns (evals/s, description dict, seconds per step)."""
@@ -350,7 +360,7 @@ def run_ours(args, rank, world, local_rank):
             "tlogs_per_s": local_evals * ref_logs / (fast_ms * 1e-3) / 1e12 if fast_ms > 0 else None,
             "note": "the kernel reaches the same result with %.0fx fewer fp64 flops and "
                     "no per-type log (exact factorisation, DESIGN.md)" % (ref_flops / flop)},
-        "traffic": None,
+        "traffic": ncu_traffic(w["name"]) if world == 1 else None,
         "algorithmic_hbm_bytes": 48 * n + 8 * (c1 - c0) * nP,
     }
     cpu_val, cpu_desc, _ = cpu_baseline(w) if world == 1 else (None, None, None)
