@@ -6,6 +6,18 @@
 # NAMESPACE: add   useDynLib(sequenza, .registration = TRUE)
 # DESCRIPTION: set NeedsCompilation: yes
 
+# The reference's post-processing of result$LPP (R/bayes.R:117-123 and :187-193), kept as
+# it is there: mean per (ploidy, cellularity) cell, axis values back from the dimnames,
+# log-sum-exp normalisation.
+.sqz.finish <- function(result) {
+    cell.mean <- tapply(result$LPP, list(result$ploidy, result$cellularity), mean)
+    top <- max(result$LPP, na.rm = TRUE)
+    log.total <- log(sum(exp(result$LPP - top))) + top
+    list(ploidy = as.numeric(rownames(cell.mean)),
+        cellularity = as.numeric(colnames(cell.mean)),
+        lpp = exp(cell.mean - log.total))
+}
+
 .sqz.priors <- function(priors.table) {
     list(CN = as.double(priors.table$CN), value = as.double(priors.table$value))
 }
@@ -51,13 +63,7 @@ baf.model.fit <- function(cellularity = seq(0.3, 1, by = 0.01),
         as.double(ploidy), as.double(cellularity), as.double(avg.depth.ratio),
         as.integer(CNt.min), as.integer(CNt.max), as.integer(CNn), p$CN, p$value,
         as.logical(ratio.priority), as.integer(n.gpus), 0L)
-    z <- tapply(result$LPP, list(result$ploidy, result$cellularity), mean)
-    x <- as.numeric(rownames(z))
-    y <- as.numeric(colnames(z))
-    max.lik <- max(result$LPP, na.rm = TRUE)
-    LogSumLik <- log(sum(exp(result$LPP - max.lik))) + max.lik
-    znorm <- exp(z - LogSumLik)
-    list(ploidy = x, cellularity = y, lpp = znorm)
+    .sqz.finish(result)
 }
 
 # R/bayes.R:126-173
@@ -107,13 +113,7 @@ mufreq.model.fit <- function(cellularity = seq(0.3, 1, by = 0.01),
         as.double(mufreq.tab$weight.ratio), as.double(ploidy), as.double(cellularity),
         as.double(avg.depth.ratio), as.integer(CNt.min), as.integer(CNt.max),
         as.integer(CNn), p$CN, p$value, as.integer(n.gpus))
-    z <- tapply(result$LPP, list(result$ploidy, result$cellularity), mean)
-    x <- as.numeric(rownames(z))
-    y <- as.numeric(colnames(z))
-    max.lik <- max(result$LPP, na.rm = TRUE)
-    LogSumLik <- log(sum(exp(result$LPP - max.lik))) + max.lik
-    znorm <- exp(z - LogSumLik)
-    list(ploidy = x, cellularity = y, lpp = znorm)
+    .sqz.finish(result)
 }
 
 # sequenza.fit (R/fit.R:1-69) is unchanged except for two optional arguments at the end
