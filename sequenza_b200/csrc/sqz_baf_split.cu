@@ -335,8 +335,8 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   double* lmid = sm + m.nc * LS;                                     // [nc] row midpoint
   double* lhw = lmid + m.nc;                                         // [nc] row half-width
   double2* stage =
-      reinterpret_cast<double2*>(sm + m.nc * LS + 2 * ((m.nc + 1) & ~1));  // [2][nc][nthr]
-  double* LBc = reinterpret_cast<double*>(stage + 2 * m.nc * nthr);  // [nc][nthr]
+      reinterpret_cast<double2*>(sm + m.nc * LS + 2 * ((m.nc + 1) & ~1));  // [3][nc][nthr]
+  double* LBc = reinterpret_cast<double*>(stage + 3 * m.nc * nthr);  // [nc][nthr]
   int* Ec = reinterpret_cast<int*>(LBc + m.nc * nthr);              // [PT][nthr]
   __shared__ double redM[4][PT];
   __shared__ long long redE[4][PT];
@@ -391,23 +391,25 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     cp_async_commit();
   };
 
+  // three-stage pipeline: the rows of a segment are requested two iterations before use
   int64_t s = cb + tid;
   double2 rk_n = make_double2(0., 0.);
   if (s < ce) {
     rk_n = a.rk[s];
     issue(0, s);
+  } else {
+    cp_async_commit();
   }
+  if (s + nthr < ce) issue(1, s + nthr);
+  else cp_async_commit();
   int it = 0, buf = 0;
   while (s < ce) {
     const double2 rk = rk_n;
     const int64_t sn = s + nthr;
-    if (sn < ce) {
-      rk_n = a.rk[sn];
-      issue(buf ^ 1, sn);
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+    if (sn < ce) rk_n = a.rk[sn];
+    if (sn + nthr < ce) issue(buf >= 1 ? buf - 1 : 2, sn + nthr);  // stage (buf + 2) % 3
+    else cp_async_commit();                                        // keep the group count even
+    cp_async_wait<2>();
     const double2* col = stage + (buf * m.nc) * nthr + tid;
 
     // (a) lower bounds; the argmin only has to be a good guess, so it is taken on the
@@ -462,7 +464,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
 
 #pragma unroll
     for (int j = 0; j < PT; ++j) P[j] *= qmin[j];
-    if ((++it & 7) == 0) {  // q < 2^127 is ample; an overflow is flagged and repaired
+    if ((++it & 15) == 0) {  // q < 2^63 is ample; an overflow is flagged and repaired
 #pragma unroll
       for (int j = 0; j < PT; ++j) {
         const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
@@ -472,7 +474,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
       }
     }
     s = sn;
-    buf ^= 1;
+    buf = buf == 2 ? 0 : buf + 1;
   }
 
   const int lane = tid & 31, warp = tid >> 5, nwarp = (nthr + 31) >> 5;
@@ -527,7 +529,7 @@ static size_t split_smem_bytes(int nc, int PT, int threads) {
 
 static size_t pruned_smem_bytes(int nc, int PT, int threads) {
   return (size_t)(nc * (PT + 2) + 2 * ((nc + 1) & ~1)) * sizeof(double) +
-         (size_t)2 * nc * threads * sizeof(double2) + (size_t)nc * threads * sizeof(double) +
+         (size_t)3 * nc * threads * sizeof(double2) + (size_t)nc * threads * sizeof(double) +
          (size_t)PT * threads * sizeof(int);
 }
 
