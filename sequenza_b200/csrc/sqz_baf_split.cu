@@ -256,9 +256,9 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
     }
 #pragma unroll
     for (int j = 0; j < PT; ++j) P[j] *= RP ? qmin[j] * sel[RP ? j : 0] : qmin[j];
-    if ((++it & 3) == 0) {
-      // every 4th segment: binary exponent -> integer column (q >= 1; four factors cannot
-      // overflow unless one is already beyond 2^255, which is caught as "bad")
+    if ((++it & 15) == 0) {
+      // every 16th segment: binary exponent -> integer column (q >= 1; sixteen factors cannot
+      // overflow unless one is already beyond 2^63, which is caught as "bad" and repaired)
 #pragma unroll
       for (int j = 0; j < PT; ++j) {
         const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
