@@ -587,8 +587,17 @@ static double tail_waste(int64_t ctas, int per_sm) {
   return 1.0 - (double)ctas / (double)(waves * slots);
 }
 
+// Candidate pruning (baf_grid_pruned_kernel) is used for few copy numbers and a sorted
+// ploidy axis.  Measured on B200: 8 copy numbers -> 1.5-2.4x over the split kernel on fine
+// and medium grids for any sd scale (tools/worstcase.py); 21 copy numbers -> no gain.
+static int prune_mode(int nc, bool monotone, bool rp) {
+  const int e = env_int("SQZ_PRUNE", -1);  // 0/1 override (experiments only)
+  if (!monotone || rp) return 0;
+  return e < 0 ? (nc <= 12 ? 1 : 0) : (e != 0);
+}
+
 static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
-                          const CnModel* m, bool rp = false) {
+                          const CnModel* m, bool rp = false, bool pruned = false) {
   GridPlan g;
   const int cand[3] = {8, 16, 32};
   double bestc = 0;
@@ -602,6 +611,9 @@ static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
       g.PT = pt;
     }
   }
+  // with pruning and a coarse ploidy axis (a 32-wide tile would span most of it and keep
+  // every copy number alive) 16-wide tiles are faster: default 91 x 61 grid, 0.57 vs 0.65 ms
+  if (pruned && nP <= 96 && g.PT == 32) g.PT = 16;
   const int pt_env = env_int("SQZ_PT", 0);  // tuning overrides (experiments only)
   if (pt_env == 8 || pt_env == 16 || (pt_env == 32 && !rp)) g.PT = pt_env;
   g.nPT = (int)((nP + g.PT - 1) / g.PT);
@@ -691,7 +703,8 @@ int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_m
   bool ok;
   int rc = build_cn_model(0, CNt_min, CNt_max, CNn, nullptr, nullptr, 0, &m, &ok);
   if (rc) return rc;
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0);
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0,
+                         prune_mode(m.nc, true, ratio_priority != 0) != 0);
   out5[0] = g.PT;
   out5[1] = g.nPT;
   out5[2] = g.nChunk;
@@ -745,7 +758,14 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   SQZ_CUDA(cudaMemcpyAsync(w.ploidy, h_ploidy, nP * sizeof(double), cudaMemcpyHostToDevice, st));
   SQZ_CUDA(cudaMemcpyAsync(w.cell, h_cell + ic0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
 
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0);
+  // candidate pruning relies on the residual being monotone over a ploidy tile
+  bool mono_up = true, mono_dn = true;
+  for (int64_t i = 1; i < nP; ++i) {
+    if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
+    if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
+  }
+  const int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune != 0);
   BafGridArgs a;
   a.S = S;
   a.seg_off = d_seg_off;
@@ -799,17 +819,6 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
                          baf_split_supported(m.nc, g.PT, g.threads) &&
                          cw_bytes >= baf_split_column_bytes(m.nc, N_total);
   if (use_split) {
-    // candidate pruning relies on the residual being monotone over a ploidy tile
-    bool mono_up = true, mono_dn = true;
-    for (int64_t i = 1; i < nP; ++i) {
-      if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
-      if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
-    }
-    // Measured on B200: with few copy numbers (config 3, 8 of them) pruning wins 1.6x; with
-    // many (config 2, 21) the per-thread bound pass and the divergence cost more than the
-    // skipped work saves, so the plain split kernel is used.  SQZ_PRUNE=0/1 overrides.
-    const int prune_env = env_int("SQZ_PRUNE", -1);
-    const bool prune = (mono_up || mono_dn) && (prune_env < 0 ? m.nc <= 12 : prune_env != 0);
     if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
     rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st,
                        prune, prof ? w.stats : nullptr);
