@@ -79,3 +79,25 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".c", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.lower(), "%s mentions the oracle" % f
+
+
+def test_header_is_plain_c_and_links(tmp_path):
+    """include/sequenza_b200.h compiles as C99, every declared entry point links, and the
+    program runs: on a CPU-only host the compute call reports SQZ_ERR_NOGPU (exit 0)."""
+    import shutil
+    import subprocess
+    gcc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no C compiler")
+    src = os.path.join(ROOT, "examples", "abi_check.c")
+    text = open(src).read()
+    for name in declared_symbols():
+        assert "(fn_t)%s" % name in text, "examples/abi_check.c does not reference %s" % name
+    exe = str(tmp_path / "abi_check")
+    libdir = os.path.dirname(_lib.SO_PATH)
+    subprocess.check_call([gcc, "-std=c99", "-Wall", "-Werror", "-pedantic",
+                           "-I" + os.path.join(ROOT, "include"), src, "-L" + libdir,
+                           "-lsequenza_b200", "-Wl,-rpath," + libdir, "-o", exe])
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "sm_100a" in out.stdout
