@@ -301,3 +301,31 @@ def test_grid_kernel_paths_agree(oracle, monkeypatch):
     monkeypatch.setenv("SQZ_PRUNE", "1")
     kw20 = dict(kw, CNt_max=20)
     assert rel_close(S.baf_grid_sums(ploidy=pl, **kw20), oracle.baf_grid_sums(ploidy=pl, **kw20))
+
+
+def test_full_size_properties_config3():
+    """BASELINE config 3 at full size (1e5 segments, CNt.max = 7, ploidy step 0.01: the
+    pruned kernel): fast == faithful on a sample of full columns, additivity over a split
+    of the segment table, and the fine-grid solution sits at the simulated truth."""
+    seg = synth_segments(100000, seed=S.synth.DEFAULT_SEED)
+    pl = S.r_seq(1, 7, 0.01)
+    cols = np.array([0.1, 0.463, 0.7, 0.999, 1.0])
+    kw = dict(cellularity=cols, ploidy=pl, priors_table=PRI)
+    fast = S.baf_grid_sums(**baf_args(seg), **kw)
+    slow = S.baf_grid_sums(mode=S.SQZ_MODE_FAITHFUL, **baf_args(seg), **kw)
+    assert np.isfinite(slow).all()
+    np.testing.assert_allclose(fast, slow, rtol=1e-12, atol=0)
+    assert int(np.argmax(fast)) == int(np.argmax(slow))
+    h = {k: (v[:33333] if isinstance(v, np.ndarray) else v) for k, v in baf_args(seg).items()}
+    t = {k: (v[33333:] if isinstance(v, np.ndarray) else v) for k, v in baf_args(seg).items()}
+    np.testing.assert_allclose(S.baf_grid_sums(**h, **kw) + S.baf_grid_sums(**t, **kw), fast,
+                               rtol=1e-13)
+    ce = S.r_seq(0.6, 0.8, 0.001)
+    fit = S.baf_model_fit(cellularity=ce, ploidy=pl, priors_table=PRI, **baf_args(seg))
+    ci = S.get_ci(fit)
+    assert abs(ci["max.cellularity"] - 0.7) <= 0.005 and abs(ci["max.ploidy"] - 2.4) <= 0.02
+    # normalised lpp: device finish (fixed-point masses) against the host steps
+    host = S.finish_model_fit(S.baf_grid_sums(cellularity=ce, ploidy=pl, priors_table=PRI,
+                                              **baf_args(seg)), pl, ce, device=False)
+    np.testing.assert_allclose(fit["lpp"], host["lpp"], rtol=1e-9, atol=1e-300)
+    assert S.get_ci(host)["confint.ploidy"] == ci["confint.ploidy"]
