@@ -148,25 +148,35 @@ def baf_model_fit_batch(samples, cellularity=None, ploidy=None, n_gpus=None, CNt
                         mode=SQZ_MODE_FAST):
     """Cohort form (BASELINE config 5): `samples` is a list of dicts with the baf.model.fit
     per-sample arguments (Bf, depth_ratio, sd_Bf, sd_ratio, weight_Bf, weight_ratio,
-    avg_depth_ratio); all samples share the grid.  One launch per device; returns one
-    list(ploidy, cellularity, lpp) per sample."""
+    avg_depth_ratio); all samples share the grid.  A cohort that is already laid out as
+    concatenated vectors can be passed as one dict with the same keys plus `seg_offsets`
+    (S + 1 values) and a per-sample `avg_depth_ratio` vector.  One launch per device;
+    returns one list(ploidy, cellularity, lpp) per sample."""
     cellularity = r_seq(0.3, 1, 0.01) if cellularity is None else cellularity
     ploidy = r_seq(1, 7, 0.1) if ploidy is None else ploidy
     pl, ce = _lib.vec(ploidy), _lib.vec(cellularity)
     keys = ("Bf", "depth_ratio", "sd_Bf", "sd_ratio", "weight_Bf", "weight_ratio")
     defaults = {"sd_Bf": 0.1, "sd_ratio": 0.5, "weight_Bf": 1, "weight_ratio": 1}
-    cols = {k: [] for k in keys}
-    off = [0]
-    for smp in samples:
-        n = _lib.vec(smp["depth_ratio"]).size
-        for k in keys:
-            cols[k].append(_lib.vec(smp.get(k, defaults.get(k)), n, k))
-        off.append(off[-1] + n)
-    cat = [np.concatenate(cols[k]) if cols[k] else np.empty(0) for k in keys]
-    offs = np.asarray(off, dtype=np.int64)
-    adr = _lib.vec([s["avg_depth_ratio"] for s in samples])
+    if isinstance(samples, dict):  # pre-concatenated cohort
+        offs = np.ascontiguousarray(samples["seg_offsets"], dtype=np.int64)
+        n_tot = int(offs[-1]) if offs.size else 0
+        cat = [_lib.vec(samples.get(k, defaults.get(k)), n_tot, k) for k in keys]
+        adr = _lib.vec(samples["avg_depth_ratio"], max(offs.size - 1, 0), "avg.depth.ratio")
+        n_samples = max(offs.size - 1, 0)
+    else:
+        cols = {k: [] for k in keys}
+        off = [0]
+        for smp in samples:
+            n = _lib.vec(smp["depth_ratio"]).size
+            for k in keys:
+                cols[k].append(_lib.vec(smp.get(k, defaults.get(k)), n, k))
+            off.append(off[-1] + n)
+        cat = [np.concatenate(cols[k]) if cols[k] else np.empty(0) for k in keys]
+        offs = np.asarray(off, dtype=np.int64)
+        adr = _lib.vec([s["avg_depth_ratio"] for s in samples])
+        n_samples = len(samples)
     pc, pv = _priors(priors_table, CNt_min, CNt_max)
-    S, G = len(samples), pl.size * ce.size
+    S, G = n_samples, pl.size * ce.size
     out = np.empty(S * G)
     if n_gpus is None:
         n_gpus = max(1, _lib.lib().sqz_device_count())

@@ -214,6 +214,14 @@ def test_grid_batch_equals_single(oracle):
         samples.append(baf_args(seg))
     fits = S.baf_model_fit_batch(samples, cellularity=ce, ploidy=pl, priors_table=PRI)
     assert len(fits) == 5
+    # the same cohort handed over as concatenated vectors + offsets
+    keys = ("Bf", "depth_ratio", "sd_Bf", "sd_ratio", "weight_Bf", "weight_ratio")
+    cohort = {k: np.concatenate([np.asarray(s[k], dtype=float) for s in samples]) for k in keys}
+    cohort["seg_offsets"] = np.cumsum([0] + [len(s["depth_ratio"]) for s in samples])
+    cohort["avg_depth_ratio"] = [s["avg_depth_ratio"] for s in samples]
+    for f, g in zip(fits, S.baf_model_fit_batch(cohort, cellularity=ce, ploidy=pl,
+                                                priors_table=PRI)):
+        np.testing.assert_array_equal(f["lpp"], g["lpp"])
     for smp, f in zip(samples, fits):
         one = S.baf_model_fit(cellularity=ce, ploidy=pl, priors_table=PRI, **smp)
         np.testing.assert_array_equal(f["lpp"], one["lpp"])

@@ -77,16 +77,34 @@ if "config5" in which:
                                        ploidy=1.5 + 3.0 * (k % 37) / 37, seed=1000 + k))
                for k in range(S_n)]
     ndev = L.sqz_device_count()
+    keys = ("Bf", "depth_ratio", "sd_Bf", "sd_ratio", "weight_Bf", "weight_ratio")
+    cohort = {k: np.concatenate([s[k] for s in samples]) for k in keys}
+    cohort["seg_offsets"] = np.arange(S_n + 1, dtype=np.int64) * n_seg
+    cohort["avg_depth_ratio"] = np.array([s["avg_depth_ratio"] for s in samples])
+    evals = float(S_n) * n_seg * ce.size * pl.size
     for g in sorted({1, ndev}):
         S.baf_model_fit_batch(samples[:8], cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=g)
+        S.baf_model_fit_batch(cohort, cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=g)
         t0 = time.perf_counter()
-        fits = S.baf_model_fit_batch(samples, cellularity=ce, ploidy=pl, priors_table=PRI,
+        fits = S.baf_model_fit_batch(cohort, cellularity=ce, ploidy=pl, priors_table=PRI,
                                      n_gpus=g)
         dt = time.perf_counter() - t0
-        evals = float(S_n) * n_seg * ce.size * pl.size
+        # the C call alone (host vectors in, host result out)
+        out = np.empty(S_n * ce.size * pl.size)
+        pc, pv = np.array([2.0]), np.array([2.0])
+        def call():
+            _lib.check(L.sqz_baf_grid_batch(
+                S_n, cohort["seg_offsets"].ctypes.data, *[_lib.ptr(cohort[k]) for k in keys],
+                _lib.ptr(pl), pl.size, _lib.ptr(ce), ce.size, _lib.ptr(cohort["avg_depth_ratio"]),
+                0, 7, 2, _lib.ptr(pc), _lib.ptr(pv), 1, 0, g, 0, _lib.ptr(out)))
+        call()
+        t0 = time.perf_counter()
+        call()
+        dc = time.perf_counter() - t0
         ok = sum(abs(S.get_ci(f)["max.cellularity"] - (0.3 + 0.6 * (k % 50) / 50)) <= 0.02
                  for k, f in enumerate(fits))
         print(json.dumps({"config": "config5 cohort: 512 samples x %d segments, grid 91 x 61, "
                           "CNt.max=7, one launch per device" % n_seg, "n_gpus": g,
-                          "s_end_to_end_host_api": dt, "evals_per_s": evals / dt,
+                          "s_python_fit_and_finish": dt, "evals_per_s_python": evals / dt,
+                          "s_sqz_baf_grid_batch": dc, "evals_per_s_c_call": evals / dc,
                           "samples_with_recovered_cellularity": int(ok)}))
