@@ -66,7 +66,8 @@ int sqz_baf_grid(const double* Bf, const double* depth_ratio, const double* sd_B
 
 /* Cohort form of B1 (BASELINE config 5): S samples share one grid.  Sample k owns
  * segments seg_offsets[k] .. seg_offsets[k+1]-1 of the concatenated vectors and
- * avg_depth_ratio[k]; lpp_sum_out is S x (nC*nP), sample-major.  One launch per device. */
+ * avg_depth_ratio[k]; lpp_sum_out is S x (nC*nP), sample-major.  One launch per device;
+ * with n_gpus > 1 and S >= n_gpus the cohort is split by sample, not by column. */
 int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
                        const double* depth_ratio, const double* sd_Bf,
                        const double* sd_ratio, const double* weight_Bf,

@@ -4,6 +4,7 @@
 // kernels on a private stream per device and copy each device's slice of the result
 // straight into the caller's output (no device-to-device gather: the consumer is the
 // R process).  The _dev entry points are thin argument checks over the launchers.
+#include <algorithm>
 #include <mutex>
 #include <vector>
 
@@ -144,39 +145,68 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
   int ndev = 0;
   int rc = usable_devices(n_gpus, &ndev);
   if (rc) return rc;
-  if (ndev > nC) ndev = (int)nC;
   std::lock_guard<std::mutex> lk(g_mu);
   DeviceGuard guard;
   const int64_t G = nP * nC;
-  // contiguous blocks of cellularity columns per device
-  std::vector<int64_t> c0(ndev + 1);
-  for (int d = 0; d <= ndev; ++d) c0[d] = nC * d / ndev;
+  // Shards.  A cohort (at least one sample per device) is cut by sample at
+  // segment-balanced boundaries, so that each device receives only its own samples'
+  // segments; otherwise every device receives all segments and takes a contiguous block
+  // of cellularity columns.
+  const bool by_sample = ndev > 1 && S >= ndev;
+  if (!by_sample && ndev > nC) ndev = (int)nC;
+  std::vector<int64_t> c0(ndev + 1), s0(ndev + 1);
+  for (int d = 0; d <= ndev; ++d) {
+    c0[d] = by_sample ? (d == 0 ? 0 : nC) : nC * d / ndev;
+    if (!by_sample) {
+      s0[d] = d == 0 ? 0 : S;
+    } else if (N == 0) {
+      s0[d] = S * d / ndev;
+    } else {
+      s0[d] = std::lower_bound(seg_off, seg_off + S + 1, N / ndev * d + N % ndev * d / ndev) -
+              seg_off;
+    }
+  }
+  s0[0] = 0;
+  s0[ndev] = S;
+  std::vector<int64_t> off_local(by_sample ? S + ndev : 0);
   for (int d = 0; d < ndev; ++d) {
+    // device d: samples [sa, sb) x columns [ca, cb)
+    const int64_t sa = by_sample ? s0[d] : 0, sb = by_sample ? s0[d + 1] : S;
+    const int64_t ca = by_sample ? 0 : c0[d], cb = by_sample ? nC : c0[d + 1];
+    const int64_t Sd = sb - sa, nCs = cb - ca;
+    if (Sd <= 0 || nCs <= 0) continue;
+    const int64_t n_lo = seg_off[sa], Nd = seg_off[sb] - n_lo;
+    const int64_t* h_off = seg_off;
+    if (by_sample) {
+      int64_t* o = off_local.data() + sa + d;
+      for (int64_t k = 0; k <= Sd; ++k) o[k] = seg_off[sa + k] - n_lo;
+      h_off = o;
+    }
     DevCtx* c;
     if ((rc = ctx_for(d, &c))) return rc;
-    const int64_t nCs = c0[d + 1] - c0[d];
-    const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
-    const size_t in_need = 6 * vbytes + a256((size_t)(S + 1) * 8) + a256((size_t)S * 8);
+    const size_t vbytes = a256((size_t)(Nd > 0 ? Nd : 1) * 8);
+    const size_t in_need = 6 * vbytes + a256((size_t)(Sd + 1) * 8) + a256((size_t)Sd * 8);
     if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
-    const size_t ws_need = baf_grid_workspace_preferred_bytes(N, S, nP, nCs,
+    const size_t ws_need = baf_grid_workspace_preferred_bytes(Nd, Sd, nP, nCs,
                                                               CNt_max - CNt_min + 1,
                                                               (size_t)2 << 30);
     if ((rc = grow(&c->ws, &c->ws_cap, ws_need))) return rc;
-    if ((rc = grow(&c->out, &c->out_cap, (size_t)(S * nCs * nP) * 8))) return rc;
+    if ((rc = grow(&c->out, &c->out_cap, (size_t)(Sd * nCs * nP) * 8))) return rc;
     char* p = (char*)c->in;
     const double* dv[6];
     for (int k = 0; k < 6; ++k) {
       dv[k] = (const double*)p;
-      if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, vec[k], (size_t)N * 8, cudaMemcpyHostToDevice, c->st));
+      if (Nd > 0)
+        SQZ_CUDA(cudaMemcpyAsync(p, vec[k] + n_lo, (size_t)Nd * 8, cudaMemcpyHostToDevice, c->st));
       p += vbytes;
     }
     int64_t* d_off = (int64_t*)p;
-    SQZ_CUDA(cudaMemcpyAsync(d_off, seg_off, (size_t)(S + 1) * 8, cudaMemcpyHostToDevice, c->st));
-    p += a256((size_t)(S + 1) * 8);
+    SQZ_CUDA(cudaMemcpyAsync(d_off, h_off, (size_t)(Sd + 1) * 8, cudaMemcpyHostToDevice, c->st));
+    p += a256((size_t)(Sd + 1) * 8);
     double* d_adr = (double*)p;
-    SQZ_CUDA(cudaMemcpyAsync(d_adr, adr, (size_t)S * 8, cudaMemcpyHostToDevice, c->st));
-    rc = baf_grid_launch(S, d_off, N, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], ploidy, nP,
-                         cell, nC, c0[d], c0[d + 1], d_adr, CNt_min, CNt_max, CNn, prior_CN,
+    SQZ_CUDA(cudaMemcpyAsync(d_adr, adr + sa, (size_t)Sd * 8, cudaMemcpyHostToDevice, c->st));
+    rc = baf_grid_launch(Sd, d_off, Nd, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], ploidy, nP,
+                         cell, nC, ca, cb, d_adr, CNt_min, CNt_max, CNn, prior_CN,
                          prior_value, n_prior, ratio_priority, mode, c->ws, c->ws_cap, c->st,
                          (double*)c->out);
     if (rc) return rc;
@@ -184,15 +214,19 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
   // Results are copied only after every device has its work queued: a device-to-host
   // copy into pageable memory blocks the calling thread until that device is done.
   for (int d = 0; d < ndev; ++d) {
+    const int64_t sa = by_sample ? s0[d] : 0, sb = by_sample ? s0[d + 1] : S;
+    const int64_t ca = by_sample ? 0 : c0[d], cb = by_sample ? nC : c0[d + 1];
+    const int64_t Sd = sb - sa, nCs = cb - ca;
+    if (Sd <= 0 || nCs <= 0) continue;
     DevCtx* c = &g_ctx[d];
-    const int64_t nCs = c0[d + 1] - c0[d];
     SQZ_CUDA(cudaSetDevice(d));
-    // device slice [S][nCs*nP] -> host [S][G] at column offset c0*nP
-    SQZ_CUDA(cudaMemcpy2DAsync(out + c0[d] * nP, (size_t)G * 8, c->out, (size_t)(nCs * nP) * 8,
-                               (size_t)(nCs * nP) * 8, (size_t)S, cudaMemcpyDeviceToHost,
-                               c->st));
+    // device slice [Sd][nCs*nP] -> host rows sa.. of [S][G] at column offset ca*nP
+    SQZ_CUDA(cudaMemcpy2DAsync(out + sa * G + ca * nP, (size_t)G * 8, c->out,
+                               (size_t)(nCs * nP) * 8, (size_t)(nCs * nP) * 8, (size_t)Sd,
+                               cudaMemcpyDeviceToHost, c->st));
   }
   for (int d = 0; d < ndev; ++d) {
+    if ((int)g_ctx.size() <= d || !g_ctx[d].live) continue;
     SQZ_CUDA(cudaSetDevice(d));
     SQZ_CUDA(cudaStreamSynchronize(g_ctx[d].st));
   }

@@ -1,0 +1,44 @@
+"""One process driving several GPUs through the host entry points (`n_gpus` > 1): a single
+sample is cut by cellularity column, a cohort by sample.  Needs two visible devices; the
+one-GPU box skips these (tools/scale_run.sh runs them on the 8-GPU box)."""
+import numpy as np
+import pytest
+
+import sequenza_b200 as S
+from sequenza_b200 import _lib
+from sequenza_b200.synth import baf_args, synth_segments
+
+pytestmark = pytest.mark.gpu
+PRI = {"CN": [2], "value": [2]}
+
+
+def _need_two():
+    if _lib.lib().sqz_device_count() < 2:
+        pytest.skip("needs two GPUs")
+
+
+def test_single_sample_column_shards():
+    _need_two()
+    seg = synth_segments(4000, seed=71)
+    ce, pl = S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1)
+    one = S.baf_grid_sums(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=1, **baf_args(seg))
+    for n in (2, _lib.lib().sqz_device_count()):
+        many = S.baf_grid_sums(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=n,
+                               **baf_args(seg))
+        np.testing.assert_allclose(many, one, rtol=1e-12, atol=0)
+
+
+@pytest.mark.parametrize("sizes", [[300, 0, 1200, 50, 700], [1] * 9, [0, 0, 40], [2500] * 16])
+def test_cohort_sample_shards(sizes):
+    _need_two()
+    ce, pl = S.r_seq(0.1, 1, 0.05), S.r_seq(1, 5, 0.25)
+    samples = []
+    for k, n in enumerate(sizes):
+        a = baf_args(synth_segments(n, seed=80 + k, cellularity=0.3 + 0.05 * (k % 10)))
+        samples.append(a)
+    one = S.baf_model_fit_batch(samples, ce, pl, n_gpus=1, priors_table=PRI)
+    for n in (2, _lib.lib().sqz_device_count()):
+        many = S.baf_model_fit_batch(samples, ce, pl, n_gpus=n, priors_table=PRI)
+        assert len(many) == len(one)
+        for a, b in zip(many, one):
+            np.testing.assert_allclose(a["lpp"], b["lpp"], rtol=1e-12, atol=0)
