@@ -430,8 +430,6 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     const int first = (int)(kbest & 63u) < nc ? (int)(kbest & 63u) : 0;
 
     double qmin[PT];
-#pragma unroll
-    for (int j = 0; j < PT; ++j) qmin[j] = INF;
     auto eval = [&](int c) {
       const double2 cwv = col[c * nthr];
       const double* l = lmr + c * LS;
@@ -443,11 +441,22 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
         if (q < qmin[j]) qmin[j] = q;  // strict <, NaN never wins
       }
     };
-    // (b) most promising copy number, (c) Qmax: largest high word plus one step of 2^-20
-    eval(first);
-    unsigned qh = 0;
+    // (b) most promising copy number: its q is the running minimum as it stands (a NaN
+    // stays, reaches the product and is flagged for repair).  (c) Qmax: x is monotone over
+    // the tile, so q = x^2 + wub peaks at one end; the larger high word plus one step of
+    // 2^-20 also covers a last-place wobble of log() in the table.
+    {
+      const double2 cwv = col[first * nthr];
+      const double* l = lmr + first * LS;
+      const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
 #pragma unroll
-    for (int j = 0; j < PT; ++j) qh = max(qh, (unsigned)__double2hiint(qmin[j]));
+      for (int j = 0; j < PT; ++j) {
+        const double x = fma(l[j], krw, erw);
+        qmin[j] = fma(x, x, cwv.x);
+      }
+    }
+    const unsigned qh = max((unsigned)__double2hiint(qmin[0]) & 0x7FFFFFFFu,
+                            (unsigned)__double2hiint(qmin[PT - 1]) & 0x7FFFFFFFu);
     const double qmax = qh >= 0x7FF00000u ? INF : __hiloint2double((int)(qh + 1u), 0);
     // (d) the copy numbers that can still lower a minimum
     unsigned long long need = 0;
