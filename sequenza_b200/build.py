@@ -14,8 +14,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsequenza_b200.so")
-SOURCES = ["sqz_api.cu", "sqz_baf_grid.cu", "sqz_baf_split.cu", "sqz_mufreq.cu",
-           "sqz_finish.cu"]
+SOURCES = ["sqz_api.cu", "sqz_baf_grid.cu", "sqz_baf_split.cu", "sqz_baf_colwarp.cu",
+           "sqz_mufreq.cu", "sqz_finish.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

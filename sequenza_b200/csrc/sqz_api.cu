@@ -189,7 +189,7 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
     if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
     const size_t ws_need = baf_grid_workspace_preferred_bytes(Nd, Sd, nP, nCs,
                                                               CNt_max - CNt_min + 1,
-                                                              (size_t)2 << 30);
+                                                              (size_t)16 << 30);
     if ((rc = grow(&c->ws, &c->ws_cap, ws_need))) return rc;
     if ((rc = grow(&c->out, &c->out_cap, (size_t)(Sd * nCs * nP) * 8))) return rc;
     char* p = (char*)c->in;

@@ -1,0 +1,361 @@
+// sqz_baf_colwarp.cu -- pruned grid kernel with one cellularity column per lane.
+//
+// baf_grid_pruned_kernel (sqz_baf_split.cu) gives every lane its own segment.  The set of
+// copy numbers that survive the bound differs from segment to segment, and a warp runs as
+// long as its slowest lane: 1.2 evaluations per thread become 2.6 per warp.  For ONE
+// segment the surviving set changes slowly with the cellularity, so here the 32 lanes of a
+// warp take 32 neighbouring columns of the same segment and ploidy tile: 1.33 evaluations
+// per warp on the same data (tools/sim/lane_mapping.py).
+//
+//   pre-pass  baf_colterm_cg_kernel: lanes = the 32 columns of a group; writes the BAF
+//             factors as [group][segment][copy number][wub | sqrt wub][32 columns], so the
+//             rows of one segment are 4 KB contiguous and each plane is read without bank
+//             conflicts.
+//   CTA       = 32 columns x WT neighbouring ploidy tiles (one per warp) x one segment chunk
+//   ring      kRing stages of kSegB segments; one elected thread fills a stage with one TMA
+//             bulk copy (plus one for the segments' ratio terms), completion on a "full"
+//             mbarrier; each warp arrives on the stage's "empty" mbarrier when done with
+//             it.  No CTA-wide barrier in the loop: warps drift apart by up to
+//             kRing - kAhead blocks, which absorbs the uneven candidate counts.  The WT
+//             warps share the stage, so the scratch is read from L2 once per WT tiles.
+//   thread    = one (column, tile): the tile's -log(ploidy term) centred on its midpoint in
+//             registers, running products in registers, exponents in shared memory
+//
+// log mr of (copy number c, ploidy j) is split as  la_c - ld_j  (R/model.R:1-7 has
+// mr = adr * A_c / D_j), so x = (la_c - ld_j - log r) k sqrt(wub) = fma(nld_j, krw, base_c):
+// the per-thread table is PT + nc numbers, not PT * nc.
+//
+// Candidate rule as in baf_grid_pruned_kernel.  The warp-uniform number of extra candidates
+// (0 in 3/4 of the iterations, 1 in 1/5) selects the loop: the minimum over candidates is
+// taken ploidy by ploidy, so no array of minima is kept next to the products.
+#include "sqz_async.cuh"
+#include "sqz_baf_grid.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+namespace {
+constexpr int kSegB = 2;   // segments per stage
+constexpr int kRing = 6;   // stages
+constexpr int kAhead = 3;  // blocks requested ahead of the one being consumed
+constexpr int kPreSeg = 256;  // segments per pre-pass CTA
+}  // namespace
+
+// ---- pre-pass: BAF factor per (column group, segment, copy number, column) --------------
+// Same arithmetic as baf_colterm_kernel (sqz_baf_split.cu); a short row scan replaces the
+// bracket search (at most 4 rows per copy number for CNt <= 7).
+__global__ void __launch_bounds__(256)
+baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_total,
+                      double* __restrict__ cwg) {
+  extern __shared__ __align__(16) double sm[];  // [T][32] model BAF of the group's columns
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int cg = blockIdx.y;
+  const int icl = min(cg * 32 + lane, nCb - 1);  // ragged last group repeats a column
+  const double cell = a.cell[ic0 + icl];
+  for (int t = warp; t < m.T; t += nwarp) {
+    int c = 0;
+    while (m.toff[c + 1] <= t) ++c;
+    sm[t * 32 + lane] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+                                        (double)m.CNn);
+  }
+  __syncthreads();
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const int64_t sb = (int64_t)blockIdx.x * kPreSeg;
+  const int64_t se = min(sb + kPreSeg, N_total);
+  for (int64_t s = sb + warp; s < se; s += nwarp) {
+    const double2 bk = a.bk[s];
+    double* out = cwg + (((int64_t)cg * N_total + s) * m.nc) * 64 + lane;
+    for (int c = 0; c < m.nc; ++c) {
+      double m0 = INF;  // min over B of |xb|: NaN never wins (R/bayes.R:70-72)
+      for (int t = m.toff[c]; t < m.toff[c + 1]; ++t) {
+        const double x0 = fma(sm[t * 32 + lane], bk.x, bk.y);
+        if (fabs(x0) < fabs(m0)) m0 = x0;
+      }
+      const double wub = fma(m0, m0, 1.0) * m.w[c];
+      out[c * 64] = wub;
+      out[c * 64 + 32] = sqrt(wub);
+    }
+  }
+}
+
+// ---- grid kernel -------------------------------------------------------------------------
+template <int PT, int NC>
+__global__ void __launch_bounds__(128, 2)
+baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
+                        int nCb, int nCG, int nTG, int64_t N_total,
+                        double* __restrict__ partM, long long* __restrict__ partE,
+                        unsigned long long* __restrict__ stats) {
+  constexpr int kSegDoubles = NC * 64;  // one segment of a column group
+  extern __shared__ __align__(128) double sm[];
+  const int nthr = blockDim.x, tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5, WT = nthr >> 5;
+  double* stage = sm;                                                        // [kRing][kSegB][NC][2][32]
+  double2* rkS = reinterpret_cast<double2*>(stage + kRing * kSegB * kSegDoubles);  // [kRing][kSegB]
+  double* lmid = reinterpret_cast<double*>(rkS + kRing * kSegB);             // [WT][NC][32]
+  double* qS = lmid + WT * NC * 32;                                          // [PT][nthr] (rare path)
+  int* Ec = reinterpret_cast<int*>(qS + PT * nthr);                          // [PT][nthr]
+  __shared__ __align__(8) unsigned long long full[kRing], empty[kRing];
+
+  int64_t b = blockIdx.x;
+  const int tg = (int)(b % nTG);
+  b /= nTG;
+  const int cg = (int)(b % nCG);
+  b /= nCG;
+  const int chunk = (int)(b % a.nChunk);
+  const int64_t smp = b / a.nChunk;
+
+  const int tile = tg * WT + warp;
+  const int nact = min(WT, a.nPT - tg * WT);  // warps of this CTA that have a tile
+  if (tid == 0) {
+    for (int s = 0; s < kRing; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], (unsigned)nact);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (tile >= a.nPT) return;
+  const int p0 = tile * PT;
+  const int icl_raw = cg * 32 + lane;
+  const int icl = min(icl_raw, nCb - 1);  // ragged last group: the lane repeats a column
+  const double cell = a.cell[ic0 + icl];
+  const double adr = a.adr[smp];
+
+  // ---- per-thread model: nld_j = -log D_j centred on the tile midpoint -----------------
+  double nld[PT];
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    const int ip = min(p0 + j, a.nP - 1);  // ragged last tile repeats the last ploidy
+    nld[j] = -log((a.ploidy[ip] / 2.0 * cell) + 1 - cell);
+  }
+  const double nmid = 0.5 * (nld[0] + nld[PT - 1]);
+#pragma unroll
+  for (int j = 0; j < PT; ++j) nld[j] -= nmid;
+  const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
+  double* lm = lmid + (warp * NC) * 32 + lane;  // [c * 32]
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const double A = (1 - cell) + ((double)(m.CNt_min + c) / (double)m.CNn * cell);
+    lm[c * 32] = log(adr * A) + nmid;
+  }
+#pragma unroll
+  for (int j = 0; j < PT; ++j) Ec[j * nthr + tid] = 0;
+
+  const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
+  const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
+  const int64_t cb = s0 + (int64_t)chunk * per;
+  const int64_t ce = min(cb + per, s1);
+  const int nblk = ce > cb ? (int)((ce - cb + kSegB - 1) / kSegB) : 0;
+  const double* cwc = cwg + (int64_t)cg * N_total * kSegDoubles;  // this group's rows
+
+  // elected thread: fill the stage of block `blk` once every warp has left its previous use
+  auto produce = [&](int blk) {
+    if (blk >= nblk) return;
+    const int s = blk % kRing, use = blk / kRing;
+    if (use > 0) mbar_wait(&empty[s], (unsigned)((use - 1) & 1));
+    const int64_t seg0 = cb + (int64_t)blk * kSegB;
+    const unsigned cnt = (unsigned)min((int64_t)kSegB, ce - seg0);
+    mbar_expect_tx(&full[s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2)));
+    tma_bulk_g2s(stage + s * kSegB * kSegDoubles, cwc + seg0 * kSegDoubles,
+                 cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[s]);
+    tma_bulk_g2s(rkS + s * kSegB, a.rk + seg0, cnt * (unsigned)sizeof(double2), &full[s]);
+  };
+
+  double P[PT];
+#pragma unroll
+  for (int j = 0; j < PT; ++j) P[j] = 1.0;
+  unsigned bad = 0, n_eval = 0;
+  int it = 0;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+
+  if (tid == 0)
+    for (int k = 0; k < kAhead; ++k) produce(k);
+  for (int blk = 0; blk < nblk; ++blk) {
+    const int s = blk % kRing;
+    if (tid == 0) produce(blk + kAhead);
+    __syncwarp();
+    mbar_wait(&full[s], (unsigned)((blk / kRing) & 1));
+    const int nsg = (int)min((int64_t)kSegB, ce - (cb + (int64_t)blk * kSegB));
+#pragma unroll 1
+    for (int sg = 0; sg < nsg; ++sg) {
+      const double2 rk = rkS[s * kSegB + sg];
+      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // wub [c*64], sqrt [c*64+32]
+
+      // (a) lower bound of every copy number over the tile; argmin on packed high words
+      const double ah = hw * fabs(rk.x);
+      double lbr[NC];
+      unsigned kbest = 0xFFFFFFFFu;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        double t = fabs(fma(lm[c * 32], rk.x, rk.y)) - ah;
+        if (t < 0.0) t = 0.0;
+        const double wv = col[c * 64];
+        const double lb = fma(wv, t * t, wv);
+        lbr[c] = lb;
+        kbest = min(kbest, ((unsigned)__double2hiint(lb) & 0xFFFFFFC0u) | (unsigned)c);
+      }
+      const int first = (int)(kbest & 63u) < NC ? (int)(kbest & 63u) : 0;
+
+      // (b) the most promising copy number; (c) Qmax from the two ends of the tile
+      const double w1 = col[first * 64], r1 = col[first * 64 + 32];
+      const double k1 = rk.x * r1;
+      const double b1 = fma(lm[first * 32], k1, rk.y * r1);
+      const double xa = fma(nld[0], k1, b1), xb = fma(nld[PT - 1], k1, b1);
+      const unsigned qh = max((unsigned)__double2hiint(fma(xa, xa, w1)) & 0x7FFFFFFFu,
+                              (unsigned)__double2hiint(fma(xb, xb, w1)) & 0x7FFFFFFFu);
+      const double qmax = qh >= 0x7FF00000u ? INF : __hiloint2double((int)(qh + 1u), 0);
+      // (d) copy numbers that can still lower a minimum
+      unsigned need = 0;
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        if (lbr[c] < qmax) need |= 1u << c;
+      need &= ~(1u << first);
+      const unsigned nx = (unsigned)__popc(need);
+      n_eval += 1u + nx;
+      const unsigned nmax = __reduce_max_sync(0xffffffffu, nx);
+
+      if (nmax == 0) {
+#pragma unroll
+        for (int j = 0; j < PT; ++j) {
+          const double x = fma(nld[j], k1, b1);
+          P[j] *= fma(x, x, w1);
+        }
+      } else {
+        // a lane with no further candidate repeats its first one: the minimum is unchanged
+        int c2 = need ? __ffs((int)need) - 1 : first;
+        need &= need - 1;
+        double w2 = col[c2 * 64], r2 = col[c2 * 64 + 32];
+        double k2 = rk.x * r2;
+        double b2 = fma(lm[c2 * 32], k2, rk.y * r2);
+        if (nmax == 1) {
+#pragma unroll
+          for (int j = 0; j < PT; ++j) {
+            const double x = fma(nld[j], k1, b1), y = fma(nld[j], k2, b2);
+            double q = fma(x, x, w1);
+            const double q2 = fma(y, y, w2);
+            if (q2 < q) q = q2;  // strict <: a NaN in the first stays and is flagged
+            P[j] *= q;
+          }
+        } else {
+          double* qs = qS + tid;  // [j * nthr]
+#pragma unroll
+          for (int j = 0; j < PT; ++j) {
+            const double x = fma(nld[j], k1, b1), y = fma(nld[j], k2, b2);
+            double q = fma(x, x, w1);
+            const double q2 = fma(y, y, w2);
+            if (q2 < q) q = q2;
+            qs[j * nthr] = q;
+          }
+          for (unsigned k = 2; k <= nmax; ++k) {
+            c2 = need ? __ffs((int)need) - 1 : first;
+            need &= need - 1;
+            w2 = col[c2 * 64];
+            r2 = col[c2 * 64 + 32];
+            k2 = rk.x * r2;
+            b2 = fma(lm[c2 * 32], k2, rk.y * r2);
+#pragma unroll
+            for (int j = 0; j < PT; ++j) {
+              const double y = fma(nld[j], k2, b2);
+              const double q2 = fma(y, y, w2);
+              if (q2 < qs[j * nthr]) qs[j * nthr] = q2;
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < PT; ++j) P[j] *= qs[j * nthr];
+        }
+      }
+
+      if ((++it & 15) == 0) {  // q < 2^63 is ample; an overflow is flagged and repaired
+#pragma unroll
+        for (int j = 0; j < PT; ++j) {
+          const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+          if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+          Ec[j * nthr + tid] += (hi >> 20) - 1023;
+          P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);  // this warp has left the stage
+  }
+
+  if (stats) {
+    if (icl_raw >= nCb) n_eval = 0;
+    for (int off = 16; off; off >>= 1) n_eval += __shfl_xor_sync(0xffffffffu, n_eval, off);
+    if (lane == 0 && n_eval) atomicAdd(stats, (unsigned long long)n_eval);
+  }
+  if (icl_raw >= nCb) return;
+  const int64_t Gs = (int64_t)a.nCs * a.nP;
+  const int64_t o = ((int64_t)chunk * a.S + smp) * Gs + (int64_t)(ic0 + icl) * a.nP + p0;
+#pragma unroll
+  for (int j = 0; j < PT; ++j) {
+    if (p0 + j < a.nP) {
+      const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+      const bool bd = ((bad >> j) & 1u) || (unsigned)(hi - 0x00100000) >= 0x7FE00000u;
+      const double v = log(__hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo));
+      partM[o + j] = bd ? __longlong_as_double(0x7FF8000000000000LL) : v;
+      partE[o + j] = (long long)Ec[j * nthr + tid] + ((hi >> 20) - 1023);
+    }
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+static size_t colwarp_smem_bytes(int NC, int PT, int threads) {
+  const int WT = threads / 32;
+  return (size_t)kRing * kSegB * NC * 64 * sizeof(double) + kRing * kSegB * sizeof(double2) +
+         (size_t)WT * NC * 32 * sizeof(double) + (size_t)PT * threads * sizeof(double) +
+         (size_t)PT * threads * sizeof(int);
+}
+
+bool baf_colwarp_supported(int nc, bool rp) { return nc == 8 && !rp; }
+
+size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
+  return (size_t)nc * 64 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
+}
+
+template <int PT>
+static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
+                          const double* cwg, int ic0, int nCb, double* partM, long long* partE,
+                          unsigned long long* stats, cudaStream_t st) {
+  const int WT = threads / 32;
+  const int nCG = (nCb + 31) / 32, nTG = (a.nPT + WT - 1) / WT;
+  const int64_t ctas = a.S * (int64_t)nCG * nTG * a.nChunk;
+  if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
+  const size_t smb = colwarp_smem_bytes(8, PT, threads);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, 8>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  baf_grid_colwarp_kernel<PT, 8><<<(unsigned)ctas, threads, smb, st>>>(
+      a, m, cwg, ic0, nCb, nCG, nTG, N_total, partM, partE, stats);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+// Pre-pass + grid kernel over the shard's columns, as many 32-column groups per launch as
+// fit cw_bytes.
+int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int threads,
+                    int64_t N_total, void* cw_buf, size_t cw_bytes, double* partM,
+                    long long* partE, cudaStream_t st, unsigned long long* stats) {
+  if (!baf_colwarp_supported(m.nc, a.rp != 0) || (threads & 31) || threads < 32 || threads > 128)
+    return fail(SQZ_ERR_ARG, "column-per-lane kernel: unsupported model or CTA size");
+  if (PT != 16 && PT != 32)
+    return fail(SQZ_ERR_ARG, "column-per-lane kernel: ploidy tile must be 16 or 32");
+  int64_t groups = (int64_t)(cw_bytes / baf_colwarp_group_bytes(m.nc, N_total));
+  if (groups < 1) return fail(SQZ_ERR_SIZE, "column-per-lane kernel needs room for 32 columns");
+  if (groups > 2047) groups = 2047;
+  double* cwg = (double*)cw_buf;
+  for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += groups * 32) {
+    const int nCb = (int)((a.nCs - ic0 < groups * 32) ? (a.nCs - ic0) : groups * 32);
+    dim3 grid((unsigned)((N_total + kPreSeg - 1) / kPreSeg), (unsigned)((nCb + 31) / 32));
+    baf_colterm_cg_kernel<<<grid, 256, (size_t)m.T * 32 * sizeof(double), st>>>(
+        a, m, (int)ic0, nCb, N_total, cwg);
+    SQZ_CUDA(cudaGetLastError());
+    const int rc = PT == 16 ? launch_colwarp<16>(a, m, threads, N_total, cwg, (int)ic0, nCb,
+                                                 partM, partE, stats, st)
+                            : launch_colwarp<32>(a, m, threads, N_total, cwg, (int)ic0, nCb,
+                                                 partM, partE, stats, st);
+    if (rc) return rc;
+  }
+  return SQZ_OK;
+}
+
+}  // namespace sqz

@@ -573,6 +573,7 @@ int profile_collect(double* ms3, int* n_calls) {
 
 struct GridPlan {
   int PT, nPT, nChunk, threads;
+  int colwarp;  // 1: column-per-lane pruned kernel (sqz_baf_colwarp.cu)
 };
 
 static int env_int(const char* name, int dflt) {
@@ -596,9 +597,57 @@ static int prune_mode(int nc, bool monotone, bool rp) {
   return e < 0 ? (nc <= 12 ? 1 : 0) : (e != 0);
 }
 
+// Chunk count of the column-per-lane kernel.  It follows the segment table only (not the
+// grid, the shard or the scratch size), so a shard of a grid and the whole grid, or two
+// scratch sizes, give the same bits.  Every warp of that kernel walks all segments of its
+// chunk: at least 64 per chunk, at most 64 chunks, fewer for a cohort (the samples already
+// fill the machine, and every chunk costs a slab of partial results).
+static int64_t colwarp_chunks(int64_t N_total, int64_t S) {
+  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+  int64_t k = avg / 64, top = S > 0 ? 2048 / S : 64;
+  if (top > 64) top = 64;
+  if (k > top) k = top;
+  return k < 1 ? 1 : k;
+}
+
+// Largest chunk count either planner may pick; the partial buffers are sized for it.
+// Segment-per-lane kernels keep >= 8 segments per thread of a 64-thread CTA.
+static int64_t max_chunks(int64_t N_total, int64_t S) {
+  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+  int64_t a = avg / (64 * 8);
+  if (a > 64) a = 64;
+  const int64_t b = colwarp_chunks(N_total, S);
+  if (b > a) a = b;
+  return a < 1 ? 1 : a;
+}
+
+static int colwarp_mode(int nc, bool rp, int64_t nCs) {
+  if (env_int("SQZ_COLWARP", 1) == 0 || !baf_colwarp_supported(nc, rp)) return 0;
+  // lanes beyond the last column of a 32-column group idle
+  const int64_t groups = (nCs + 31) / 32;
+  return env_int("SQZ_COLWARP", -1) == 1 || nCs * 10 >= groups * 32 * 6;
+}
+
+// Plan for the column-per-lane kernel.
+static GridPlan plan_colwarp(int64_t N_total, int64_t S, int64_t nP) {
+  GridPlan g;
+  g.colwarp = 1;
+  g.PT = nP <= 96 ? 16 : 32;
+  const int pt_env = env_int("SQZ_PT", 0);
+  if (pt_env == 16 || pt_env == 32) g.PT = pt_env;
+  g.nPT = (int)((nP + g.PT - 1) / g.PT);
+  const int WT = g.nPT < 4 ? g.nPT : 4;
+  g.threads = 32 * WT;
+  g.nChunk = (int)colwarp_chunks(N_total, S);
+  const int ch_env = env_int("SQZ_CHUNKS", 0);
+  if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
+  return g;
+}
+
 static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
                           const CnModel* m, bool rp = false, bool pruned = false) {
   GridPlan g;
+  g.colwarp = 0;
   const int cand[3] = {8, 16, 32};
   double bestc = 0;
   g.PT = 32;
@@ -649,7 +698,7 @@ static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
   }
   g.nChunk = (int)best;
   const int ch_env = env_int("SQZ_CHUNKS", 0);
-  if (ch_env >= 1 && ch_env <= 64) g.nChunk = ch_env;
+  if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
   return g;
 }
 
@@ -676,12 +725,7 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   };
   const size_t n = (size_t)(N_total > 0 ? N_total : 1);
   const size_t items = (size_t)(S * nCs * nP > 0 ? S * nCs * nP : 1);
-  // partials are sized for the largest chunk count the planner may pick (64), bounded
-  // by what the segment count allows (>= 8 segments per thread, >= 64 threads)
-  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
-  int64_t want = avg / (64 * 8);
-  if (want > 64) want = 64;
-  if (want < 1) want = 1;
+  const int64_t want = max_chunks(N_total, S);
   w.rk = (double2*)take(n * sizeof(double2));
   w.bk = (double2*)take(n * sizeof(double2));
   w.nB = (int*)take((size_t)(S > 0 ? S : 1) * sizeof(int));
@@ -703,8 +747,10 @@ int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_m
   bool ok;
   int rc = build_cn_model(0, CNt_min, CNt_max, CNn, nullptr, nullptr, 0, &m, &ok);
   if (rc) return rc;
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0,
-                         prune_mode(m.nc, true, ratio_priority != 0) != 0);
+  const bool prune = prune_mode(m.nc, true, ratio_priority != 0) != 0;
+  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune);
+  if (prune && N_total > 0 && colwarp_mode(m.nc, ratio_priority != 0, nCs))
+    g = plan_colwarp(N_total, S, nP);  // as baf_grid_launch decides given the preferred workspace
   out5[0] = g.PT;
   out5[1] = g.nPT;
   out5[2] = g.nChunk;
@@ -724,6 +770,7 @@ size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP
   if (n_copy_numbers < 1 || n_copy_numbers > kMaxCN || nCs < 1) return base;
   const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
   size_t cols = (size_t)nCs;
+  if (baf_colwarp_supported(n_copy_numbers, false)) cols = (cols + 31) & ~(size_t)31;
   if (cap_bytes > 0 && cols * per_col > cap_bytes) cols = cap_bytes / per_col;
   if (cols < 1) cols = 1;
   return base + align256(cols * per_col);
@@ -764,8 +811,16 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
     if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
   }
-  const int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
+  int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
   GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune != 0);
+  // pre-pass scratch behind the fixed part of the workspace
+  char* cw_buf = (char*)workspace + w.bytes;
+  const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
+  if (prune && N_total > 0 && colwarp_mode(m.nc, ratio_priority != 0, nCs) &&
+      cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total)) {
+    g = plan_colwarp(N_total, S, nP);  // column-per-lane kernel: room for >= 32 columns
+    prune = 2;
+  }
   BafGridArgs a;
   a.S = S;
   a.seg_off = d_seg_off;
@@ -813,17 +868,17 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[1], st));
   // Split path when the workspace has room for at least one column of pre-pass output
   // (sqz_baf_grid_workspace_preferred_bytes); fused kernel otherwise.
-  char* cw_buf = (char*)workspace + w.bytes;
-  const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
   const bool use_split = env_int("SQZ_SPLIT", 1) != 0 && N_total > 0 &&
-                         baf_split_supported(m.nc, g.PT, g.threads) &&
+                         (prune == 2 || baf_split_supported(m.nc, g.PT, g.threads)) &&
                          cw_bytes >= baf_split_column_bytes(m.nc, N_total);
   if (use_split) {
     if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
-    rc = baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM, w.partE, st,
-                       prune, prof ? w.stats : nullptr);
+    rc = prune == 2 ? baf_colwarp_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
+                                      w.partE, st, prof ? w.stats : nullptr)
+                    : baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
+                                    w.partE, st, prune, prof ? w.stats : nullptr);
     if (prof) {
-      prof->path = prune ? 2 : 1;
+      prof->path = prune == 2 ? 3 : (prune ? 2 : 1);
       SQZ_CUDA(cudaMemcpyAsync(&prof->n_eval, w.stats, sizeof(unsigned long long),
                                cudaMemcpyDeviceToHost, st));
     }

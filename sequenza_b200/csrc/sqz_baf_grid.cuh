@@ -27,6 +27,15 @@ size_t baf_split_column_bytes(int nc, int64_t N_total);
 bool baf_split_supported(int nc, int PT, int threads);
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, bool prune, unsigned long long* stats);
+                  cudaStream_t st, int prune, unsigned long long* stats);
+
+// Pruned grid kernel with one cellularity column per lane (sqz_baf_colwarp.cu), with its
+// own pre-pass and scratch layout: baf_colwarp_group_bytes per group of 32 columns.
+// threads = 32 x (ploidy tiles per CTA).
+bool baf_colwarp_supported(int nc, bool rp);
+size_t baf_colwarp_group_bytes(int nc, int64_t N_total);
+int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int threads,
+                    int64_t N_total, void* cw_buf, size_t cw_bytes, double* partM,
+                    long long* partE, cudaStream_t st, unsigned long long* stats);
 
 }  // namespace sqz

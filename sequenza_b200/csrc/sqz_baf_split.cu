@@ -22,6 +22,7 @@
 // holds the SMSP math dispatch for ~2.2 cycles and they do not overlap
 // (tools/microbench*.cu), so the kernel is built to minimise math instructions per
 // (copy number, ploidy): 5 here against 6.8 in the fused kernel.
+#include "sqz_async.cuh"
 #include "sqz_baf_grid.cuh"
 #include "../../include/sequenza_b200.h"
 
@@ -84,48 +85,6 @@ baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
   }
 }
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() {
-  asm volatile("cp.async.commit_group;" ::: "memory");
-}
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-// ---- TMA (bulk async copy) + mbarrier helpers ------------------------------------------
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(
-                   (unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
-                   (unsigned)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-  const unsigned addr = (unsigned)__cvta_generic_to_shared(bar);
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(addr), "r"(parity) : "memory");
-}
-// one contiguous row global -> shared, completion counted in bytes on the mbarrier
-__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gsrc, unsigned bytes,
-                                             unsigned long long* bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-      ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes),
-      "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
-}
-
 // ---- grid kernel ------------------------------------------------------------------------
 // Staging of the pre-pass rows: one elected thread issues a bulk async copy (TMA, 1-D) per
 // copy number for the CTA's next 128 segments -- each row of the scratch is contiguous over
@@ -159,7 +118,7 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   if (tid == 0) {
     mbar_init(&bar[0], 1);
     mbar_init(&bar[1], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_fence_init();
   }
 
   // log model depth ratio of this (cellularity, ploidy tile): R/model.R:1-7, :49-56
@@ -594,8 +553,9 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
 // Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, bool prune, unsigned long long* stats) {
-  if (prune && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = false;
+                  cudaStream_t st, int prune, unsigned long long* stats) {
+  if (prune == 2) prune = 1;  // the column-per-lane kernel is driven by baf_colwarp_run
+  if (prune == 1 && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = 0;
   const size_t per_col = baf_split_column_bytes(m.nc, N_total);
   int64_t nCb_max = (int64_t)(cw_bytes / per_col);
   if (nCb_max < 1) return fail(SQZ_ERR_SIZE, "split path needs room for one column");

@@ -71,7 +71,7 @@ class BafGridDevice:
         self.h_off_t = torch.from_numpy(self.h_offsets).pin_memory()
         self.upload()
         self._ws = None
-        self.ws_cap = 2 << 30  # bytes of pre-pass scratch the grid fit may use per call
+        self.ws_cap = 16 << 30  # bytes of pre-pass scratch the grid fit may use per call
 
     def upload(self):
         """Host (pinned) -> device copies of every per-segment input; returns bytes moved."""

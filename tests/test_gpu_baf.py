@@ -289,15 +289,17 @@ def test_grid_kernel_paths_agree(oracle, monkeypatch):
     kw = dict(cellularity=ce, priors_table=PRI, **baf_args(seg))
     ref = oracle.baf_grid_sums(ploidy=pl, **kw)
     for env in ({"SQZ_SPLIT": "0"}, {"SQZ_PRUNE": "0"}, {"SQZ_PRUNE": "1"},
-                {"SQZ_PRUNE": "1", "SQZ_PT": "16"}, {"SQZ_PRUNE": "1", "SQZ_PT": "8"}):
-        for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT"):
+                {"SQZ_PRUNE": "1", "SQZ_PT": "16"}, {"SQZ_PRUNE": "1", "SQZ_PT": "8"},
+                {"SQZ_COLWARP": "0"}, {"SQZ_COLWARP": "0", "SQZ_PT": "16"},
+                {"SQZ_COLWARP": "1", "SQZ_PT": "32"}, {"SQZ_COLWARP": "1", "SQZ_PT": "16"}):
+        for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT", "SQZ_COLWARP"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         got = S.baf_grid_sums(ploidy=pl, **kw)
         assert rel_close(got, ref), env
         assert int(np.argmax(got)) == int(np.argmax(ref)), env
-    for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT"):
+    for k in ("SQZ_SPLIT", "SQZ_PRUNE", "SQZ_PT", "SQZ_COLWARP"):
         monkeypatch.delenv(k, raising=False)
     # descending and unsorted ploidy vectors (pruning needs a monotone tile; unsorted input
     # falls back to the plain split kernel), duplicated values
@@ -309,6 +311,37 @@ def test_grid_kernel_paths_agree(oracle, monkeypatch):
     monkeypatch.setenv("SQZ_PRUNE", "1")
     kw20 = dict(kw, CNt_max=20)
     assert rel_close(S.baf_grid_sums(ploidy=pl, **kw20), oracle.baf_grid_sums(ploidy=pl, **kw20))
+
+
+@pytest.mark.parametrize("n_seg", [1, 3, 4, 257, 2050])
+@pytest.mark.parametrize("grid", [(46, 121), (33, 40), (5, 20), (91, 5), (64, 601)])
+def test_grid_column_lane_kernel(oracle, monkeypatch, n_seg, grid):
+    """Column-per-lane pruned kernel (sqz_baf_colwarp.cu), forced on: ragged column groups,
+    fewer than four ploidy tiles per CTA, ragged last tile, segment counts that are not a
+    multiple of the stage size, several chunks; and the same call as a cohort."""
+    monkeypatch.setenv("SQZ_COLWARP", "1")
+    nC, nP = grid
+    if n_seg * nC * nP > 2e7:
+        pytest.skip("oracle time")
+    ce = np.linspace(0.05, 1.0, nC)
+    pl = np.linspace(1.0, 7.0, nP)
+    seg = synth_segments(n_seg, seed=300 + n_seg)
+    kw = dict(cellularity=ce, ploidy=pl, priors_table=PRI)
+    ref = oracle.baf_grid_sums(**baf_args(seg), **kw)
+    got = S.baf_grid_sums(**baf_args(seg), **kw)
+    assert rel_close(got, ref)
+    assert int(np.nanargmax(got)) == int(np.nanargmax(ref))
+    if n_seg == 2050 and nP <= 121:
+        monkeypatch.setenv("SQZ_CHUNKS", "7")
+        assert rel_close(S.baf_grid_sums(**baf_args(seg), **kw), ref)
+        monkeypatch.delenv("SQZ_CHUNKS")
+        other = synth_segments(77, seed=9, cellularity=0.4)
+        fits = S.baf_model_fit_batch([baf_args(seg), baf_args(other), baf_args(seg)], ce, pl,
+                                     priors_table=PRI, n_gpus=1)
+        one = S.baf_model_fit(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=1,
+                              **baf_args(other))
+        np.testing.assert_allclose(fits[1]["lpp"], one["lpp"], rtol=1e-9, atol=1e-300)
+        np.testing.assert_array_equal(fits[0]["lpp"], fits[2]["lpp"])
 
 
 def test_full_size_properties_config3():
