@@ -7,17 +7,18 @@
 // warp take 32 neighbouring columns of the same segment and ploidy tile: 1.33 evaluations
 // per warp on the same data (tools/sim/lane_mapping.py).
 //
-//   pre-pass  baf_colterm_cg_kernel: lanes = the 32 columns of a group; writes the BAF
-//             factors as [group][segment][copy number][wub | sqrt wub][32 columns], so the
-//             rows of one segment are 4 KB contiguous and each plane is read without bank
-//             conflicts.
-//   CTA       = 32 columns x WT neighbouring ploidy tiles (one per warp) x one segment chunk
-//   ring      kRing stages of kSegB segments; one elected thread fills a stage with one TMA
-//             bulk copy (plus one for the segments' ratio terms), completion on a "full"
-//             mbarrier; each warp arrives on the stage's "empty" mbarrier when done with
-//             it.  No CTA-wide barrier in the loop: warps drift apart by up to
-//             kRing - kAhead blocks, which absorbs the uneven candidate counts.  The WT
-//             warps share the stage, so the scratch is read from L2 once per WT tiles.
+//   pre-pass  baf_colterm_cg_kernel: lanes = the 32 columns of a group; writes sqrt(wub) as
+//             [group][segment][copy number][32 columns]: the rows of one segment are 2 KB
+//             contiguous.  wub itself is the square (one DMUL where it is needed), which
+//             halves the scratch and its traffic.
+//   CTA       = ONE warp: 32 columns x one ploidy tile x one segment chunk.  Warps of
+//             different tiles cost different amounts (the candidate counts differ), so
+//             nothing is shared between them and the hardware scheduler balances them;
+//             the tiles of one (group, chunk) are neighbours in the grid and find each
+//             other's rows in L2.
+//   ring      kRing stages of kSegB segments; lane 0 fills a stage with one TMA bulk copy
+//             (plus one for the segments' ratio terms) and completion is counted on an
+//             mbarrier; the stage is refilled as soon as the warp has left it.
 //   thread    = one (column, tile): the tile's -log(ploidy term) centred on its midpoint in
 //             registers, running products in registers, exponents in shared memory
 //
@@ -36,8 +37,7 @@ namespace sqz {
 
 namespace {
 constexpr int kSegB = 2;   // segments per stage
-constexpr int kRing = 6;   // stages
-constexpr int kAhead = 3;  // blocks requested ahead of the one being consumed
+constexpr int kRing = 3;   // stages: two in flight while one is consumed
 constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 }  // namespace
 
@@ -64,57 +64,48 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
   const int64_t se = min(sb + kPreSeg, N_total);
   for (int64_t s = sb + warp; s < se; s += nwarp) {
     const double2 bk = a.bk[s];
-    double* out = cwg + (((int64_t)cg * N_total + s) * m.nc) * 64 + lane;
+    double* out = cwg + (((int64_t)cg * N_total + s) * m.nc) * 32 + lane;
     for (int c = 0; c < m.nc; ++c) {
       double m0 = INF;  // min over B of |xb|: NaN never wins (R/bayes.R:70-72)
       for (int t = m.toff[c]; t < m.toff[c + 1]; ++t) {
         const double x0 = fma(sm[t * 32 + lane], bk.x, bk.y);
         if (fabs(x0) < fabs(m0)) m0 = x0;
       }
-      const double wub = fma(m0, m0, 1.0) * m.w[c];
-      out[c * 64] = wub;
-      out[c * 64 + 32] = sqrt(wub);
+      out[c * 32] = sqrt(fma(m0, m0, 1.0) * m.w[c]);
     }
   }
 }
 
 // ---- grid kernel -------------------------------------------------------------------------
 template <int PT, int NC>
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(32, 8)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
-                        int nCb, int nCG, int nTG, int64_t N_total,
-                        double* __restrict__ partM, long long* __restrict__ partE,
-                        unsigned long long* __restrict__ stats) {
-  constexpr int kSegDoubles = NC * 64;  // one segment of a column group
-  extern __shared__ __align__(128) double sm[];
-  const int nthr = blockDim.x, tid = threadIdx.x;
-  const int lane = tid & 31, warp = tid >> 5, WT = nthr >> 5;
-  double* stage = sm;                                                        // [kRing][kSegB][NC][2][32]
+                        int nCb, int nCG, int64_t N_total, double* __restrict__ partM,
+                        long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
+  constexpr int kSegDoubles = NC * 32;  // one segment of a column group
+  constexpr int nthr = 32;
+  extern __shared__ __align__(16) double sm[];
+  const int lane = threadIdx.x, tid = threadIdx.x;
+  double* stage = sm;                                                               // [kRing][kSegB][NC][32]
   double2* rkS = reinterpret_cast<double2*>(stage + kRing * kSegB * kSegDoubles);  // [kRing][kSegB]
-  double* lmid = reinterpret_cast<double*>(rkS + kRing * kSegB);             // [WT][NC][32]
-  double* qS = lmid + WT * NC * 32;                                          // [PT][nthr] (rare path)
-  int* Ec = reinterpret_cast<int*>(qS + PT * nthr);                          // [PT][nthr]
-  __shared__ __align__(8) unsigned long long full[kRing], empty[kRing];
+  double* lm = reinterpret_cast<double*>(rkS + kRing * kSegB) + lane;              // [NC][32]
+  double* qS = lm - lane + NC * 32;                                                 // [PT][32] (rare path)
+  int* Ec = reinterpret_cast<int*>(qS + PT * 32);                                   // [PT][32]
+  __shared__ __align__(8) unsigned long long full[kRing];
 
   int64_t b = blockIdx.x;
-  const int tg = (int)(b % nTG);
-  b /= nTG;
+  const int tile = (int)(b % a.nPT);
+  b /= a.nPT;
   const int cg = (int)(b % nCG);
   b /= nCG;
   const int chunk = (int)(b % a.nChunk);
   const int64_t smp = b / a.nChunk;
 
-  const int tile = tg * WT + warp;
-  const int nact = min(WT, a.nPT - tg * WT);  // warps of this CTA that have a tile
-  if (tid == 0) {
-    for (int s = 0; s < kRing; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], (unsigned)nact);
-    }
+  if (lane == 0) {
+    for (int s = 0; s < kRing; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
-  __syncthreads();
-  if (tile >= a.nPT) return;
+  __syncwarp();
   const int p0 = tile * PT;
   const int icl_raw = cg * 32 + lane;
   const int icl = min(icl_raw, nCb - 1);  // ragged last group: the lane repeats a column
@@ -132,7 +123,6 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 #pragma unroll
   for (int j = 0; j < PT; ++j) nld[j] -= nmid;
   const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
-  double* lm = lmid + (warp * NC) * 32 + lane;  // [c * 32]
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     const double A = (1 - cell) + ((double)(m.CNt_min + c) / (double)m.CNn * cell);
@@ -148,11 +138,10 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const int nblk = ce > cb ? (int)((ce - cb + kSegB - 1) / kSegB) : 0;
   const double* cwc = cwg + (int64_t)cg * N_total * kSegDoubles;  // this group's rows
 
-  // elected thread: fill the stage of block `blk` once every warp has left its previous use
-  auto produce = [&](int blk) {
+  // lane 0: request block `blk` into its stage (the warp has left the stage's last use)
+  auto fetch = [&](int blk) {
     if (blk >= nblk) return;
-    const int s = blk % kRing, use = blk / kRing;
-    if (use > 0) mbar_wait(&empty[s], (unsigned)((use - 1) & 1));
+    const int s = blk % kRing;
     const int64_t seg0 = cb + (int64_t)blk * kSegB;
     const unsigned cnt = (unsigned)min((int64_t)kSegB, ce - seg0);
     mbar_expect_tx(&full[s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2)));
@@ -168,18 +157,20 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   int it = 0;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
-  if (tid == 0)
-    for (int k = 0; k < kAhead; ++k) produce(k);
+  if (lane == 0)
+    for (int k = 0; k < kRing - 1; ++k) fetch(k);
   for (int blk = 0; blk < nblk; ++blk) {
     const int s = blk % kRing;
-    if (tid == 0) produce(blk + kAhead);
+    // the stage of the previous block is free (every lane has left it): request the block
+    // that goes there, kRing - 1 ahead of the one consumed now
     __syncwarp();
+    if (lane == 0) fetch(blk + kRing - 1);
     mbar_wait(&full[s], (unsigned)((blk / kRing) & 1));
     const int nsg = (int)min((int64_t)kSegB, ce - (cb + (int64_t)blk * kSegB));
 #pragma unroll 1
     for (int sg = 0; sg < nsg; ++sg) {
       const double2 rk = rkS[s * kSegB + sg];
-      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // wub [c*64], sqrt [c*64+32]
+      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // sqrt(wub) [c * 32]
 
       // (a) lower bound of every copy number over the tile; argmin on packed high words
       const double ah = hw * fabs(rk.x);
@@ -189,15 +180,15 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
       for (int c = 0; c < NC; ++c) {
         double t = fabs(fma(lm[c * 32], rk.x, rk.y)) - ah;
         if (t < 0.0) t = 0.0;
-        const double wv = col[c * 64];
-        const double lb = fma(wv, t * t, wv);
+        const double rv = col[c * 32], u = rv * t;
+        const double lb = fma(u, u, rv * rv);
         lbr[c] = lb;
         kbest = min(kbest, ((unsigned)__double2hiint(lb) & 0xFFFFFFC0u) | (unsigned)c);
       }
       const int first = (int)(kbest & 63u) < NC ? (int)(kbest & 63u) : 0;
 
       // (b) the most promising copy number; (c) Qmax from the two ends of the tile
-      const double w1 = col[first * 64], r1 = col[first * 64 + 32];
+      const double r1 = col[first * 32], w1 = r1 * r1;
       const double k1 = rk.x * r1;
       const double b1 = fma(lm[first * 32], k1, rk.y * r1);
       const double xa = fma(nld[0], k1, b1), xb = fma(nld[PT - 1], k1, b1);
@@ -224,7 +215,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         // a lane with no further candidate repeats its first one: the minimum is unchanged
         int c2 = need ? __ffs((int)need) - 1 : first;
         need &= need - 1;
-        double w2 = col[c2 * 64], r2 = col[c2 * 64 + 32];
+        double r2 = col[c2 * 32], w2 = r2 * r2;
         double k2 = rk.x * r2;
         double b2 = fma(lm[c2 * 32], k2, rk.y * r2);
         if (nmax == 1) {
@@ -249,8 +240,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
           for (unsigned k = 2; k <= nmax; ++k) {
             c2 = need ? __ffs((int)need) - 1 : first;
             need &= need - 1;
-            w2 = col[c2 * 64];
-            r2 = col[c2 * 64 + 32];
+            r2 = col[c2 * 32];
+            w2 = r2 * r2;
             k2 = rk.x * r2;
             b2 = fma(lm[c2 * 32], k2, rk.y * r2);
 #pragma unroll
@@ -275,8 +266,6 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         }
       }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[s]);  // this warp has left the stage
   }
 
   if (stats) {
@@ -300,43 +289,43 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 }
 
 // ---- host side ---------------------------------------------------------------------------
-static size_t colwarp_smem_bytes(int NC, int PT, int threads) {
-  const int WT = threads / 32;
-  return (size_t)kRing * kSegB * NC * 64 * sizeof(double) + kRing * kSegB * sizeof(double2) +
-         (size_t)WT * NC * 32 * sizeof(double) + (size_t)PT * threads * sizeof(double) +
-         (size_t)PT * threads * sizeof(int);
+static size_t colwarp_smem_bytes(int NC, int PT) {
+  return (size_t)kRing * kSegB * NC * 32 * sizeof(double) + kRing * kSegB * sizeof(double2) +
+         (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(double) +
+         (size_t)PT * 32 * sizeof(int);
 }
 
 bool baf_colwarp_supported(int nc, bool rp) { return nc == 8 && !rp; }
 
 size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
-  return (size_t)nc * 64 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
+  return (size_t)nc * 32 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
 }
 
 template <int PT>
-static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
+static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_total,
                           const double* cwg, int ic0, int nCb, double* partM, long long* partE,
                           unsigned long long* stats, cudaStream_t st) {
-  const int WT = threads / 32;
-  const int nCG = (nCb + 31) / 32, nTG = (a.nPT + WT - 1) / WT;
-  const int64_t ctas = a.S * (int64_t)nCG * nTG * a.nChunk;
+  const int nCG = (nCb + 31) / 32;
+  const int64_t ctas = a.S * (int64_t)nCG * a.nPT * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  const size_t smb = colwarp_smem_bytes(8, PT, threads);
+  const size_t smb = colwarp_smem_bytes(8, PT);
   SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, 8>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-  baf_grid_colwarp_kernel<PT, 8><<<(unsigned)ctas, threads, smb, st>>>(
-      a, m, cwg, ic0, nCb, nCG, nTG, N_total, partM, partE, stats);
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, 8>,
+                                cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+  baf_grid_colwarp_kernel<PT, 8><<<(unsigned)ctas, 32, smb, st>>>(
+      a, m, cwg, ic0, nCb, nCG, N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
 
 // Pre-pass + grid kernel over the shard's columns, as many 32-column groups per launch as
 // fit cw_bytes.
-int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int threads,
-                    int64_t N_total, void* cw_buf, size_t cw_bytes, double* partM,
-                    long long* partE, cudaStream_t st, unsigned long long* stats) {
-  if (!baf_colwarp_supported(m.nc, a.rp != 0) || (threads & 31) || threads < 32 || threads > 128)
-    return fail(SQZ_ERR_ARG, "column-per-lane kernel: unsupported model or CTA size");
+int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_total,
+                    void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
+                    cudaStream_t st, unsigned long long* stats) {
+  if (!baf_colwarp_supported(m.nc, a.rp != 0))
+    return fail(SQZ_ERR_ARG, "column-per-lane kernel: unsupported model");
   if (PT != 16 && PT != 32)
     return fail(SQZ_ERR_ARG, "column-per-lane kernel: ploidy tile must be 16 or 32");
   int64_t groups = (int64_t)(cw_bytes / baf_colwarp_group_bytes(m.nc, N_total));
@@ -349,10 +338,10 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int threads,
     baf_colterm_cg_kernel<<<grid, 256, (size_t)m.T * 32 * sizeof(double), st>>>(
         a, m, (int)ic0, nCb, N_total, cwg);
     SQZ_CUDA(cudaGetLastError());
-    const int rc = PT == 16 ? launch_colwarp<16>(a, m, threads, N_total, cwg, (int)ic0, nCb,
-                                                 partM, partE, stats, st)
-                            : launch_colwarp<32>(a, m, threads, N_total, cwg, (int)ic0, nCb,
-                                                 partM, partE, stats, st);
+    const int rc = PT == 16 ? launch_colwarp<16>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE,
+                                                 stats, st)
+                            : launch_colwarp<32>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE,
+                                                 stats, st);
     if (rc) return rc;
   }
   return SQZ_OK;

@@ -636,8 +636,7 @@ static GridPlan plan_colwarp(int64_t N_total, int64_t S, int64_t nP) {
   const int pt_env = env_int("SQZ_PT", 0);
   if (pt_env == 16 || pt_env == 32) g.PT = pt_env;
   g.nPT = (int)((nP + g.PT - 1) / g.PT);
-  const int WT = g.nPT < 4 ? g.nPT : 4;
-  g.threads = 32 * WT;
+  g.threads = 32;  // one warp per CTA
   g.nChunk = (int)colwarp_chunks(N_total, S);
   const int ch_env = env_int("SQZ_CHUNKS", 0);
   if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
@@ -770,7 +769,15 @@ size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP
   if (n_copy_numbers < 1 || n_copy_numbers > kMaxCN || nCs < 1) return base;
   const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
   size_t cols = (size_t)nCs;
-  if (baf_colwarp_supported(n_copy_numbers, false)) cols = (cols + 31) & ~(size_t)31;
+  if (baf_colwarp_supported(n_copy_numbers, false)) {
+    // the column-per-lane kernel keeps half as much per column, in whole 32-column groups;
+    // if a call cannot use it (ratio.priority, unsorted ploidies) the split path runs the
+    // columns in two batches
+    size_t want = ((cols + 31) / 32) * baf_colwarp_group_bytes(n_copy_numbers, N_total);
+    if (want < per_col) want = per_col;
+    if (cap_bytes > 0 && want > cap_bytes) want = cap_bytes;
+    return base + align256(want);
+  }
   if (cap_bytes > 0 && cols * per_col > cap_bytes) cols = cap_bytes / per_col;
   if (cols < 1) cols = 1;
   return base + align256(cols * per_col);
@@ -873,8 +880,8 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
                          cw_bytes >= baf_split_column_bytes(m.nc, N_total);
   if (use_split) {
     if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
-    rc = prune == 2 ? baf_colwarp_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
-                                      w.partE, st, prof ? w.stats : nullptr)
+    rc = prune == 2 ? baf_colwarp_run(a, m, g.PT, N_total, cw_buf, cw_bytes, w.partM, w.partE,
+                                      st, prof ? w.stats : nullptr)
                     : baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
                                     w.partE, st, prune, prof ? w.stats : nullptr);
     if (prof) {

@@ -31,11 +31,11 @@ int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, i
 
 // Pruned grid kernel with one cellularity column per lane (sqz_baf_colwarp.cu), with its
 // own pre-pass and scratch layout: baf_colwarp_group_bytes per group of 32 columns.
-// threads = 32 x (ploidy tiles per CTA).
+// One warp per CTA.
 bool baf_colwarp_supported(int nc, bool rp);
 size_t baf_colwarp_group_bytes(int nc, int64_t N_total);
-int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int threads,
-                    int64_t N_total, void* cw_buf, size_t cw_bytes, double* partM,
-                    long long* partE, cudaStream_t st, unsigned long long* stats);
+int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_total,
+                    void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
+                    cudaStream_t st, unsigned long long* stats);
 
 }  // namespace sqz
