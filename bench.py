@@ -320,8 +320,17 @@ def run_ours(args, rank, world, local_rank):
     # and tile for the bounds.
     pre = (2.0 * T + 14.0 * n_c) / nP
     kernel_names = {0: "baf_grid_fast_kernel (fused)", 1: "baf_grid_split_kernel",
-                    2: "baf_grid_pruned_kernel"}
-    if kpath.value == 2 and ncall.value > 0:
+                    2: "baf_grid_pruned_kernel", 3: "baf_grid_colwarp_kernel"}
+    if kpath.value == 3 and ncall.value > 0:
+        # column-per-lane kernel: per (segment, tile) 6 fp64 + 4 integer instructions per
+        # copy number for the bounds and ~10 + ~10 to set up the first candidate; the first
+        # candidate costs 2 DFMA + DMUL per ploidy (no minimum), every further one that the
+        # warp evaluates 2 DFMA + DSETP + 2 FSEL
+        cand = n_cand.value / (float(ncall.value) * n * (c1 - c0) * nPT)  # per segment, tile
+        inst = 3.0 + (cand - 1.0) * 3.0 + (6.0 * n_c + 10.0) / PT + pre
+        math = inst + (cand - 1.0) * 2.0 + (4.0 * n_c + 10.0) / PT
+        flop = 5.0 + (cand - 1.0) * 5.0 + (8.0 * n_c + 14.0) / PT + 1.5 * pre
+    elif kpath.value == 2 and ncall.value > 0:
         cand = n_cand.value / (float(ncall.value) * n * (c1 - c0) * nPT)  # per segment, tile
         inst = cand * (3.0 + 2.0 / PT) + 1 + 6.0 * n_c / PT + pre
         math = inst + cand * 2.0 + 4.0 * n_c / PT
@@ -337,7 +346,8 @@ def run_ours(args, rank, world, local_rank):
     ref_logs = n_c + T
     roofline = {
         "bound": "fp64",
-        "kernel": "%s<%d> (+ baf_colterm pre-pass)" % (kernel_names.get(kpath.value, "?"), PT),
+        "kernel": "%s<%d> (+ baf_colterm%s pre-pass)" % (
+            kernel_names.get(kpath.value, "?"), PT, "_cg" if kpath.value == 3 else ""),
         "copy_numbers_evaluated_per_segment_and_tile": cand, "copy_numbers": n_c,
         "achieved": ach, "peak": peak.value, "unit": "TFLOP/s",
         "frac": (ach / peak.value) if ach and peak.value else None,
@@ -362,10 +372,11 @@ def run_ours(args, rank, world, local_rank):
                     "no per-type log (exact factorisation, DESIGN.md)" % (ref_flops / flop)},
         "traffic": ncu_traffic(w["name"]) if world == 1 else None,
         "algorithmic_hbm_bytes": 48 * n + 8 * (c1 - c0) * nP,
-        "traffic_note": "the grid kernel reads the pre-pass scratch (16 B x copy numbers x "
-                        "segments per column) once; that scratch replaces recomputing the BAF "
-                        "term in every ploidy tile and runs at ~0.7 TB/s, far below the HBM "
-                        "peak: the kernel is bound by math dispatch, not by this traffic",
+        "traffic_note": "the grid kernel reads the pre-pass scratch (16 B, or 8 B for the "
+                        "column-per-lane kernel, x copy numbers x segments per column) once "
+                        "per ploidy tile, mostly from L2; that scratch replaces recomputing "
+                        "the BAF term in every ploidy tile; its DRAM traffic is far below the "
+                        "HBM peak: the kernel is bound by math dispatch, not by this traffic",
     }
     cpu_val, cpu_desc, _ = cpu_baseline(w) if world == 1 else (None, None, None)
     line = {
@@ -385,9 +396,10 @@ def run_ours(args, rank, world, local_rank):
                 "api": "sqz_baf_grid (host pointers)" if world == 1 else
                        "BafGridDevice.upload + sqz_baf_grid_dev + NCCL all-gather + D2H"},
         "gpu_launches": 5 * args.steps,
-        "gpu_launches_note": "per step: baf_prep, baf_colterm, baf_grid_split, "
-                             "baf_grid_finalize, baf_grid_faithful (repair), per column "
-                             "batch; + torch copy kernels for N>1",
+        "gpu_launches_note": "per step: baf_prep, the pre-pass (baf_colterm or baf_colterm_cg), "
+                             "the grid kernel named in roofline.kernel, baf_grid_finalize, "
+                             "baf_grid_faithful (repair); all columns fit one batch of the "
+                             "pre-pass scratch here; + torch copy kernels for N>1",
         "roofline": roofline,
         "fit_wall_ms": e2e_ms,
         "solution": {"cellularity": float(ce[int(np.argmax(lpp_sum)) // nP]) if world == 1 else None,

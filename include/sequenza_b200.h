@@ -280,8 +280,10 @@ int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, 
 int sqz_profile_enable(int on);
 int sqz_profile_collect(double* ms3, int* n_calls);
 /* Call before sqz_profile_collect: *path = kernel path of the recorded calls (0 fused, 1
- * split, 2 split with candidate pruning); *n_eval = (segment, ploidy tile, copy number)
- * evaluations the pruned kernel actually made, summed over the recorded calls. */
+ * split, 2 split with candidate pruning, one segment per lane, 3 candidate pruning with
+ * one cellularity column per lane); *n_eval = (segment, ploidy tile, copy number)
+ * evaluations the pruned kernel actually made, summed over the recorded calls (path 3:
+ * per column, counting what the column's warp executed). */
 int sqz_profile_counters(int* path, unsigned long long* n_eval);
 
 #ifdef __cplusplus

@@ -135,55 +135,65 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
   const int64_t cb = s0 + (int64_t)chunk * per;
   const int64_t ce = min(cb + per, s1);
-  const int nblk = ce > cb ? (int)((ce - cb + kSegB - 1) / kSegB) : 0;
   const double* cwc = cwg + (int64_t)cg * N_total * kSegDoubles;  // this group's rows
 
-  // lane 0: request block `blk` into its stage (the warp has left the stage's last use)
-  auto fetch = [&](int blk) {
-    if (blk >= nblk) return;
-    const int s = blk % kRing;
-    const int64_t seg0 = cb + (int64_t)blk * kSegB;
-    const unsigned cnt = (unsigned)min((int64_t)kSegB, ce - seg0);
-    mbar_expect_tx(&full[s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2)));
-    tma_bulk_g2s(stage + s * kSegB * kSegDoubles, cwc + seg0 * kSegDoubles,
-                 cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[s]);
-    tma_bulk_g2s(rkS + s * kSegB, a.rk + seg0, cnt * (unsigned)sizeof(double2), &full[s]);
+  // Requests run ahead of the consumption by kRing - 1 blocks; the state below is
+  // warp-uniform, lane 0 issues.  A stage is requested again only after every lane has
+  // left it (the __syncwarp before the call).
+  const double* f_src = cwc + cb * kSegDoubles;
+  const double2* f_rk = a.rk + cb;
+  int64_t f_left = ce - cb;  // segments not yet requested
+  int f_s = 0;
+  auto fetch = [&]() {
+    if (f_left <= 0) return;
+    const unsigned cnt = f_left < kSegB ? (unsigned)f_left : (unsigned)kSegB;
+    if (lane == 0) {
+      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2)));
+      tma_bulk_g2s(stage + f_s * kSegB * kSegDoubles, f_src,
+                   cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[f_s]);
+      tma_bulk_g2s(rkS + f_s * kSegB, f_rk, cnt * (unsigned)sizeof(double2), &full[f_s]);
+    }
+    f_src += kSegB * kSegDoubles;
+    f_rk += kSegB;
+    f_left -= kSegB;
+    f_s = f_s == kRing - 1 ? 0 : f_s + 1;
   };
 
   double P[PT];
 #pragma unroll
   for (int j = 0; j < PT; ++j) P[j] = 1.0;
   unsigned bad = 0, n_eval = 0;
-  int it = 0;
-  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  // Upper bound of the binary exponent the products may have gained since the last
+  // renormalisation: every factor is at most the first candidate's q at a tile end.
+  int grown = 0;
 
-  if (lane == 0)
-    for (int k = 0; k < kRing - 1; ++k) fetch(k);
-  for (int blk = 0; blk < nblk; ++blk) {
-    const int s = blk % kRing;
-    // the stage of the previous block is free (every lane has left it): request the block
-    // that goes there, kRing - 1 ahead of the one consumed now
+  for (int k = 0; k < kRing - 1; ++k) fetch();
+  int s = 0;
+  unsigned phase = 0;
+  for (int64_t left = ce - cb; left > 0; left -= kSegB) {
     __syncwarp();
-    if (lane == 0) fetch(blk + kRing - 1);
-    mbar_wait(&full[s], (unsigned)((blk / kRing) & 1));
-    const int nsg = (int)min((int64_t)kSegB, ce - (cb + (int64_t)blk * kSegB));
+    fetch();
+    mbar_wait(&full[s], phase);
+    const int nsg = left < kSegB ? (int)left : kSegB;
 #pragma unroll 1
     for (int sg = 0; sg < nsg; ++sg) {
       const double2 rk = rkS[s * kSegB + sg];
       const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // sqrt(wub) [c * 32]
 
-      // (a) lower bound of every copy number over the tile; argmin on packed high words
-      const double ah = hw * fabs(rk.x);
-      double lbr[NC];
+      // (a) lower bound of every copy number over the tile (high words are enough: Qmax
+      // below has a zero low word); argmin on the high words with the index packed in.
+      // max(t0, 0) = t0/2 + |t0/2| with exact halves: one DADD, no compare and selects.
+      const double hx = 0.5 * rk.x, hy = 0.5 * rk.y;
+      const double ah = hw * fabs(hx);
+      unsigned lbh[NC];
       unsigned kbest = 0xFFFFFFFFu;
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        double t = fabs(fma(lm[c * 32], rk.x, rk.y)) - ah;
-        if (t < 0.0) t = 0.0;
+        const double t0 = fabs(fma(lm[c * 32], hx, hy)) - ah;
+        const double t = t0 + fabs(t0);
         const double rv = col[c * 32], u = rv * t;
-        const double lb = fma(u, u, rv * rv);
-        lbr[c] = lb;
-        kbest = min(kbest, ((unsigned)__double2hiint(lb) & 0xFFFFFFC0u) | (unsigned)c);
+        lbh[c] = (unsigned)__double2hiint(fma(u, u, rv * rv));
+        kbest = min(kbest, (lbh[c] & 0xFFFFFFC0u) | (unsigned)c);
       }
       const int first = (int)(kbest & 63u) < NC ? (int)(kbest & 63u) : 0;
 
@@ -194,16 +204,18 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
       const double xa = fma(nld[0], k1, b1), xb = fma(nld[PT - 1], k1, b1);
       const unsigned qh = max((unsigned)__double2hiint(fma(xa, xa, w1)) & 0x7FFFFFFFu,
                               (unsigned)__double2hiint(fma(xb, xb, w1)) & 0x7FFFFFFFu);
-      const double qmax = qh >= 0x7FF00000u ? INF : __hiloint2double((int)(qh + 1u), 0);
-      // (d) copy numbers that can still lower a minimum
+      // (d) copy numbers that can still lower a minimum: lb < Qmax = (qh + 1, 0), i.e. the
+      // high word of lb is at most qh; Qmax = +Inf keeps every finite bound
+      const unsigned qcap = qh >= 0x7FF00000u ? 0x7FEFFFFFu : qh;
+      grown += (int)(qh >> 20) - 1021;
       unsigned need = 0;
 #pragma unroll
       for (int c = 0; c < NC; ++c)
-        if (lbr[c] < qmax) need |= 1u << c;
+        if (lbh[c] <= qcap) need |= 1u << c;
       need &= ~(1u << first);
       const unsigned nx = (unsigned)__popc(need);
-      n_eval += 1u + nx;
       const unsigned nmax = __reduce_max_sync(0xffffffffu, nx);
+      n_eval += 1u + nmax;  // what the warp executes: every lane follows the longest list
 
       if (nmax == 0) {
 #pragma unroll
@@ -256,7 +268,10 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         }
       }
 
-      if ((++it & 15) == 0) {  // q < 2^63 is ample; an overflow is flagged and repaired
+      // the products are renormalised (binary exponent -> integer column) before they can
+      // overflow; q >= 1, so they never underflow
+      if (__any_sync(0xffffffffu, grown > 900)) {
+        grown = 0;
 #pragma unroll
         for (int j = 0; j < PT; ++j) {
           const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
@@ -265,6 +280,10 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
           P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
         }
       }
+    }
+    if (++s == kRing) {
+      s = 0;
+      phase ^= 1u;
     }
   }
 

@@ -621,20 +621,30 @@ static int64_t max_chunks(int64_t N_total, int64_t S) {
   return a < 1 ? 1 : a;
 }
 
-static int colwarp_mode(int nc, bool rp, int64_t nCs) {
-  if (env_int("SQZ_COLWARP", 1) == 0 || !baf_colwarp_supported(nc, rp)) return 0;
-  // lanes beyond the last column of a 32-column group idle
+// Ploidy tile of the column-per-lane kernel, or 0 when the segment-per-lane pruned kernel is
+// the better choice.  The column-per-lane kernel runs one warp per (32 columns, tile, chunk)
+// and there are 8 warp slots per SM: it wins when those units fill the machine for several
+// waves (measured: tools/colwarp_vs_pruned.py), and when few lanes of the last 32-column
+// group idle.  32-wide tiles when there are enough units, else 16-wide (twice the units).
+static int colwarp_tile(int nc, bool rp, int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
+  const int e = env_int("SQZ_COLWARP", -1);  // 0/1 override (experiments and tests only)
+  if (e == 0 || !baf_colwarp_supported(nc, rp) || N_total <= 0) return 0;
+  const int pt_env = env_int("SQZ_PT", 0);
+  if (e == 1) return (pt_env == 16 || pt_env == 32) ? pt_env : (nP <= 96 ? 16 : 32);
   const int64_t groups = (nCs + 31) / 32;
-  return env_int("SQZ_COLWARP", -1) == 1 || nCs * 10 >= groups * 32 * 6;
+  if (nCs * 10 < groups * 32 * 6) return 0;
+  const int64_t slots = 148 * 8, ch = colwarp_chunks(N_total, S);
+  const int64_t u32 = S * groups * ((nP + 31) / 32) * ch, u16 = S * groups * ((nP + 15) / 16) * ch;
+  if (nP > 96 && u32 >= 6 * slots) return 32;
+  if (u16 >= 3 * slots) return 16;
+  return 0;
 }
 
 // Plan for the column-per-lane kernel.
-static GridPlan plan_colwarp(int64_t N_total, int64_t S, int64_t nP) {
+static GridPlan plan_colwarp(int64_t N_total, int64_t S, int64_t nP, int PT) {
   GridPlan g;
   g.colwarp = 1;
-  g.PT = nP <= 96 ? 16 : 32;
-  const int pt_env = env_int("SQZ_PT", 0);
-  if (pt_env == 16 || pt_env == 32) g.PT = pt_env;
+  g.PT = PT;
   g.nPT = (int)((nP + g.PT - 1) / g.PT);
   g.threads = 32;  // one warp per CTA
   g.nChunk = (int)colwarp_chunks(N_total, S);
@@ -748,8 +758,9 @@ int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_m
   if (rc) return rc;
   const bool prune = prune_mode(m.nc, true, ratio_priority != 0) != 0;
   GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune);
-  if (prune && N_total > 0 && colwarp_mode(m.nc, ratio_priority != 0, nCs))
-    g = plan_colwarp(N_total, S, nP);  // as baf_grid_launch decides given the preferred workspace
+  const int cw_pt = prune ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
+  if (cw_pt) g = plan_colwarp(N_total, S, nP, cw_pt);  // as baf_grid_launch decides given
+                                                       // the preferred workspace
   out5[0] = g.PT;
   out5[1] = g.nPT;
   out5[2] = g.nChunk;
@@ -823,9 +834,9 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   // pre-pass scratch behind the fixed part of the workspace
   char* cw_buf = (char*)workspace + w.bytes;
   const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
-  if (prune && N_total > 0 && colwarp_mode(m.nc, ratio_priority != 0, nCs) &&
-      cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total)) {
-    g = plan_colwarp(N_total, S, nP);  // column-per-lane kernel: room for >= 32 columns
+  const int cw_pt = prune ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
+  if (cw_pt && cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total)) {
+    g = plan_colwarp(N_total, S, nP, cw_pt);  // column-per-lane kernel: room for >= 32 columns
     prune = 2;
   }
   BafGridArgs a;
