@@ -7,10 +7,12 @@
 // warp take 32 neighbouring columns of the same segment and ploidy tile: 1.33 evaluations
 // per warp on the same data (tools/sim/lane_mapping.py).
 //
-//   pre-pass  baf_colterm_cg_kernel: lanes = the 32 columns of a group; writes sqrt(wub) as
-//             [group][segment][copy number][32 columns]: the rows of one segment are 2 KB
-//             contiguous.  wub itself is the square (one DMUL where it is needed), which
-//             halves the scratch and its traffic.
+//   pre-pass  baf_colterm_cg_kernel: lanes = the 32 columns of a group; writes ONE number per
+//             (segment, copy number, column) as [group][segment][copy number][32 columns],
+//             so the rows of one segment are contiguous (2 KB for CNt 0..7).  For 8 copy
+//             numbers it is sqrt(wub) and wub is the square (one DMUL where needed); for
+//             21 it is wub and the square root is taken for the one or two copy numbers
+//             that get evaluated.  Half the scratch and traffic of the (wub, sqrt) pairs.
 //   CTA       = ONE warp: 32 columns x one ploidy tile x one segment chunk.  Warps of
 //             different tiles cost different amounts (the candidate counts differ), so
 //             nothing is shared between them and the hardware scheduler balances them;
@@ -36,7 +38,6 @@
 namespace sqz {
 
 namespace {
-constexpr int kSegB = 2;   // segments per stage
 constexpr int kRing = 3;   // stages: two in flight while one is consumed
 constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 }  // namespace
@@ -45,9 +46,12 @@ constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 // Same arithmetic as baf_colterm_kernel (sqz_baf_split.cu); a short row scan replaces the
 // bracket search (at most 4 rows per copy number for CNt <= 7).
 __global__ void __launch_bounds__(256)
-baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_total,
+baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_total, int store_sqrt,
                       double* __restrict__ cwg) {
-  extern __shared__ __align__(16) double sm[];  // [T][32] model BAF of the group's columns
+  extern __shared__ __align__(16) double sm[];
+  double* mb = sm;                   // [T][32] model BAF of the group's columns (R/model.R:9-14)
+  double* b_a = sm + m.T * 32;       // [nc][32] model BAF at B = 0
+  double* b_invd = b_a + m.nc * 32;  // [nc][32] 1 / (model BAF step per unit of B)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int cg = blockIdx.y;
   const int icl = min(cg * 32 + lane, nCb - 1);  // ragged last group repeats a column
@@ -55,8 +59,13 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
   for (int t = warp; t < m.T; t += nwarp) {
     int c = 0;
     while (m.toff[c + 1] <= t) ++c;
-    sm[t * 32 + lane] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
+    mb[t * 32 + lane] = theoretical_baf((double)(m.CNt_min + c), (double)(t - m.toff[c]), cell,
                                         (double)m.CNn);
+  }
+  for (int c = warp; c < m.nc; c += nwarp) {
+    const double den = ((double)(m.CNt_min + c) * cell) + (double)m.CNn * (1 - cell);
+    b_a[c * 32 + lane] = (1 - cell) / den;
+    b_invd[c * 32 + lane] = den / cell;
   }
   __syncthreads();
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
@@ -64,14 +73,28 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
   const int64_t se = min(sb + kPreSeg, N_total);
   for (int64_t s = sb + warp; s < se; s += nwarp) {
     const double2 bk = a.bk[s];
+    const double Bf = a.Bf[s];
     double* out = cwg + (((int64_t)cg * N_total + s) * m.nc) * 32 + lane;
     for (int c = 0; c < m.nc; ++c) {
-      double m0 = INF;  // min over B of |xb|: NaN never wins (R/bayes.R:70-72)
-      for (int t = m.toff[c]; t < m.toff[c + 1]; ++t) {
-        const double x0 = fma(sm[t * 32 + lane], bk.x, bk.y);
+      // min over B of |xb|: NaN never wins (R/bayes.R:70-72); long rows read only the two
+      // rows that bracket Bf (see baf_colterm_kernel)
+      const int t0 = m.toff[c], nb = m.toff[c + 1] - t0;
+      double m0 = INF;
+      if (nb > 3) {
+        int b0 = __double2int_rd((Bf - b_a[c * 32 + lane]) * b_invd[c * 32 + lane]);  // NaN -> 0
+        b0 = max(0, min(b0, nb - 2));
+        const double x0 = fma(mb[(t0 + b0) * 32 + lane], bk.x, bk.y);
+        const double x1 = fma(mb[(t0 + b0 + 1) * 32 + lane], bk.x, bk.y);
         if (fabs(x0) < fabs(m0)) m0 = x0;
+        if (fabs(x1) < fabs(m0)) m0 = x1;
+      } else {
+        for (int t = t0; t < t0 + nb; ++t) {
+          const double x0 = fma(mb[t * 32 + lane], bk.x, bk.y);
+          if (fabs(x0) < fabs(m0)) m0 = x0;
+        }
       }
-      out[c * 32] = sqrt(fma(m0, m0, 1.0) * m.w[c]);
+      const double wub = fma(m0, m0, 1.0) * m.w[c];
+      out[c * 32] = store_sqrt ? sqrt(wub) : wub;
     }
   }
 }
@@ -83,6 +106,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
                         int nCb, int nCG, int64_t N_total, double* __restrict__ partM,
                         long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int kSegDoubles = NC * 32;  // one segment of a column group
+  constexpr int kSegB = NC <= 8 ? 2 : 1;  // segments per stage (a stage is at most 5.25 KB)
+  constexpr bool SQ = NC <= 8;            // the scratch holds sqrt(wub) (else wub)
   constexpr int nthr = 32;
   extern __shared__ __align__(16) double sm[];
   const int lane = threadIdx.x, tid = threadIdx.x;
@@ -191,14 +216,15 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
       for (int c = 0; c < NC; ++c) {
         const double t0 = fabs(fma(lm[c * 32], hx, hy)) - ah;
         const double t = t0 + fabs(t0);
-        const double rv = col[c * 32], u = rv * t;
-        lbh[c] = (unsigned)__double2hiint(fma(u, u, rv * rv));
+        const double rv = col[c * 32], u = SQ ? rv * t : t * t;
+        lbh[c] = (unsigned)__double2hiint(SQ ? fma(u, u, rv * rv) : fma(rv, u, rv));
         kbest = min(kbest, (lbh[c] & 0xFFFFFFC0u) | (unsigned)c);
       }
       const int first = (int)(kbest & 63u) < NC ? (int)(kbest & 63u) : 0;
 
       // (b) the most promising copy number; (c) Qmax from the two ends of the tile
-      const double r1 = col[first * 32], w1 = r1 * r1;
+      const double v1 = col[first * 32];
+      const double r1 = SQ ? v1 : sqrt(v1), w1 = SQ ? v1 * v1 : v1;
       const double k1 = rk.x * r1;
       const double b1 = fma(lm[first * 32], k1, rk.y * r1);
       const double xa = fma(nld[0], k1, b1), xb = fma(nld[PT - 1], k1, b1);
@@ -227,7 +253,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         // a lane with no further candidate repeats its first one: the minimum is unchanged
         int c2 = need ? __ffs((int)need) - 1 : first;
         need &= need - 1;
-        double r2 = col[c2 * 32], w2 = r2 * r2;
+        double v2 = col[c2 * 32];
+        double r2 = SQ ? v2 : sqrt(v2), w2 = SQ ? v2 * v2 : v2;
         double k2 = rk.x * r2;
         double b2 = fma(lm[c2 * 32], k2, rk.y * r2);
         if (nmax == 1) {
@@ -252,8 +279,9 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
           for (unsigned k = 2; k <= nmax; ++k) {
             c2 = need ? __ffs((int)need) - 1 : first;
             need &= need - 1;
-            r2 = col[c2 * 32];
-            w2 = r2 * r2;
+            v2 = col[c2 * 32];
+            r2 = SQ ? v2 : sqrt(v2);
+            w2 = SQ ? v2 * v2 : v2;
             k2 = rk.x * r2;
             b2 = fma(lm[c2 * 32], k2, rk.y * r2);
 #pragma unroll
@@ -309,30 +337,32 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 
 // ---- host side ---------------------------------------------------------------------------
 static size_t colwarp_smem_bytes(int NC, int PT) {
-  return (size_t)kRing * kSegB * NC * 32 * sizeof(double) + kRing * kSegB * sizeof(double2) +
+  const int segb = NC <= 8 ? 2 : 1;
+  return (size_t)kRing * segb * NC * 32 * sizeof(double) + kRing * segb * sizeof(double2) +
          (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(double) +
          (size_t)PT * 32 * sizeof(int);
 }
 
-bool baf_colwarp_supported(int nc, bool rp) { return nc == 8 && !rp; }
+// CNt 0..7 (sequenza.fit, R/bayes.R:40) and CNt 0..20 (sequenza.results, R/analysis.R)
+bool baf_colwarp_supported(int nc, bool rp) { return (nc == 8 || nc == 21) && !rp; }
 
 size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
   return (size_t)nc * 32 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
 }
 
-template <int PT>
+template <int PT, int NC>
 static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_total,
                           const double* cwg, int ic0, int nCb, double* partM, long long* partE,
                           unsigned long long* stats, cudaStream_t st) {
   const int nCG = (nCb + 31) / 32;
   const int64_t ctas = a.S * (int64_t)nCG * a.nPT * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  const size_t smb = colwarp_smem_bytes(8, PT);
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, 8>,
+  const size_t smb = colwarp_smem_bytes(NC, PT);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, 8>,
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-  baf_grid_colwarp_kernel<PT, 8><<<(unsigned)ctas, 32, smb, st>>>(
+  baf_grid_colwarp_kernel<PT, NC><<<(unsigned)ctas, 32, smb, st>>>(
       a, m, cwg, ic0, nCb, nCG, N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
@@ -351,16 +381,24 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
   if (groups < 1) return fail(SQZ_ERR_SIZE, "column-per-lane kernel needs room for 32 columns");
   if (groups > 2047) groups = 2047;
   double* cwg = (double*)cw_buf;
+  const size_t pre_smem = (size_t)(m.T + 2 * m.nc) * 32 * sizeof(double);
   for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += groups * 32) {
     const int nCb = (int)((a.nCs - ic0 < groups * 32) ? (a.nCs - ic0) : groups * 32);
     dim3 grid((unsigned)((N_total + kPreSeg - 1) / kPreSeg), (unsigned)((nCb + 31) / 32));
-    baf_colterm_cg_kernel<<<grid, 256, (size_t)m.T * 32 * sizeof(double), st>>>(
-        a, m, (int)ic0, nCb, N_total, cwg);
+    baf_colterm_cg_kernel<<<grid, 256, pre_smem, st>>>(a, m, (int)ic0, nCb, N_total,
+                                                       m.nc <= 8 ? 1 : 0, cwg);
     SQZ_CUDA(cudaGetLastError());
-    const int rc = PT == 16 ? launch_colwarp<16>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE,
-                                                 stats, st)
-                            : launch_colwarp<32>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE,
-                                                 stats, st);
+    int rc;
+#define SQZ_CW(PTV, NCV) \
+  rc = launch_colwarp<PTV, NCV>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE, stats, st)
+    if (m.nc == 8) {
+      if (PT == 16) SQZ_CW(16, 8);
+      else SQZ_CW(32, 8);
+    } else {
+      if (PT == 16) SQZ_CW(16, 21);
+      else SQZ_CW(32, 21);
+    }
+#undef SQZ_CW
     if (rc) return rc;
   }
   return SQZ_OK;

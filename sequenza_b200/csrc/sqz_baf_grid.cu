@@ -635,6 +635,9 @@ static int colwarp_tile(int nc, bool rp, int64_t N_total, int64_t S, int64_t nP,
   if (nCs * 10 < groups * 32 * 6) return 0;
   const int64_t slots = 148 * 8, ch = colwarp_chunks(N_total, S);
   const int64_t u32 = S * groups * ((nP + 31) / 32) * ch, u16 = S * groups * ((nP + 15) / 16) * ch;
+  if (nc > 8)  // CNt 0..20: a coarse ploidy axis keeps 4-6 copy numbers alive per warp and
+               // the plain split kernel is as fast (91 x 61 grid: 1.44 vs 1.50 ms)
+    return (nP >= 200 && u16 >= 2 * slots) ? 16 : 0;
   if (nP > 96 && u32 >= 6 * slots) return 32;
   if (u16 >= 3 * slots) return 16;
   return 0;
@@ -758,7 +761,8 @@ int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_m
   if (rc) return rc;
   const bool prune = prune_mode(m.nc, true, ratio_priority != 0) != 0;
   GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune);
-  const int cw_pt = prune ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
+  const int cw_pt = env_int("SQZ_PRUNE", 1) != 0
+                        ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
   if (cw_pt) g = plan_colwarp(N_total, S, nP, cw_pt);  // as baf_grid_launch decides given
                                                        // the preferred workspace
   out5[0] = g.PT;
@@ -781,11 +785,11 @@ size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP
   const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
   size_t cols = (size_t)nCs;
   if (baf_colwarp_supported(n_copy_numbers, false)) {
-    // the column-per-lane kernel keeps half as much per column, in whole 32-column groups;
-    // if a call cannot use it (ratio.priority, unsorted ploidies) the split path runs the
-    // columns in two batches
+    // whichever kernel the call ends up with runs all columns in one batch: the
+    // segment-per-lane kernels keep 16 bytes per (column, copy number, segment), the
+    // column-per-lane kernel 8, in whole 32-column groups
     size_t want = ((cols + 31) / 32) * baf_colwarp_group_bytes(n_copy_numbers, N_total);
-    if (want < per_col) want = per_col;
+    if (want < cols * per_col) want = cols * per_col;
     if (cap_bytes > 0 && want > cap_bytes) want = cap_bytes;
     return base + align256(want);
   }
@@ -834,7 +838,8 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   // pre-pass scratch behind the fixed part of the workspace
   char* cw_buf = (char*)workspace + w.bytes;
   const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
-  const int cw_pt = prune ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
+  const int cw_pt = (mono_up || mono_dn) && env_int("SQZ_PRUNE", 1) != 0
+                        ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
   if (cw_pt && cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total)) {
     g = plan_colwarp(N_total, S, nP, cw_pt);  // column-per-lane kernel: room for >= 32 columns
     prune = 2;

@@ -313,20 +313,21 @@ def test_grid_kernel_paths_agree(oracle, monkeypatch):
     assert rel_close(S.baf_grid_sums(ploidy=pl, **kw20), oracle.baf_grid_sums(ploidy=pl, **kw20))
 
 
+@pytest.mark.parametrize("cn_max", [7, 20])
 @pytest.mark.parametrize("n_seg", [1, 3, 4, 257, 2050])
 @pytest.mark.parametrize("grid", [(46, 121), (33, 40), (5, 20), (91, 5), (64, 601)])
-def test_grid_column_lane_kernel(oracle, monkeypatch, n_seg, grid):
+def test_grid_column_lane_kernel(oracle, monkeypatch, n_seg, grid, cn_max):
     """Column-per-lane pruned kernel (sqz_baf_colwarp.cu), forced on: ragged column groups,
     fewer than four ploidy tiles per CTA, ragged last tile, segment counts that are not a
     multiple of the stage size, several chunks; and the same call as a cohort."""
     monkeypatch.setenv("SQZ_COLWARP", "1")
     nC, nP = grid
-    if n_seg * nC * nP > 2e7:
+    if n_seg * nC * nP * (5 if cn_max == 20 else 1) > 2e7:
         pytest.skip("oracle time")
     ce = np.linspace(0.05, 1.0, nC)
     pl = np.linspace(1.0, 7.0, nP)
-    seg = synth_segments(n_seg, seed=300 + n_seg)
-    kw = dict(cellularity=ce, ploidy=pl, priors_table=PRI)
+    seg = synth_segments(n_seg, seed=300 + n_seg, cn_max=cn_max)
+    kw = dict(cellularity=ce, ploidy=pl, priors_table=PRI, CNt_max=cn_max)
     ref = oracle.baf_grid_sums(**baf_args(seg), **kw)
     got = S.baf_grid_sums(**baf_args(seg), **kw)
     assert rel_close(got, ref)
@@ -337,9 +338,9 @@ def test_grid_column_lane_kernel(oracle, monkeypatch, n_seg, grid):
         monkeypatch.delenv("SQZ_CHUNKS")
         other = synth_segments(77, seed=9, cellularity=0.4)
         fits = S.baf_model_fit_batch([baf_args(seg), baf_args(other), baf_args(seg)], ce, pl,
-                                     priors_table=PRI, n_gpus=1)
+                                     priors_table=PRI, n_gpus=1, CNt_max=cn_max)
         one = S.baf_model_fit(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=1,
-                              **baf_args(other))
+                              CNt_max=cn_max, **baf_args(other))
         np.testing.assert_allclose(fits[1]["lpp"], one["lpp"], rtol=1e-9, atol=1e-300)
         np.testing.assert_array_equal(fits[0]["lpp"], fits[2]["lpp"])
 

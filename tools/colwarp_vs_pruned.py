@@ -10,14 +10,17 @@ from sequenza_b200.synth import synth_segments, baf_args
 PRI = {"CN": [2], "value": [2]}
 
 
+CN_MAX = int(sys.argv[1]) if len(sys.argv) > 1 else 7  # 20: the other kernel is the split one
+
+
 def timed(dev, pl, ce, env):
     for k in ("SQZ_COLWARP", "SQZ_PT"):
         os.environ.pop(k, None)
     os.environ.update(env)
-    dev.run(pl, ce, priors_table=PRI); torch.cuda.synchronize()
+    dev.run(pl, ce, priors_table=PRI, CNt_max=CN_MAX); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(3): dev.run(pl, ce, priors_table=PRI)
+    for _ in range(3): dev.run(pl, ce, priors_table=PRI, CNt_max=CN_MAX)
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / 3
 
@@ -30,7 +33,7 @@ for name, ce, pl in cases:
         for scale in (0.1, 1.0, 10.0):
             if scale != 1.0 and n != 30000:
                 continue
-            seg = synth_segments(n, seed=3)
+            seg = synth_segments(n, seed=3, cn_max=CN_MAX)
             seg["sd_ratio"] = seg["sd_ratio"] * scale
             seg["sd_Bf"] = seg["sd_Bf"] * scale
             dev = BafGridDevice(**baf_args(seg))
@@ -39,7 +42,7 @@ for name, ce, pl in cases:
                 timed(dev, pl, ce, {"SQZ_COLWARP": "1", "SQZ_PT": "16"}),
                 timed(dev, pl, ce, {"SQZ_COLWARP": "1", "SQZ_PT": "32"})), flush=True)
 # lane efficiency: column counts that leave part of the last 32-column group idle
-seg = synth_segments(30000, seed=3)
+seg = synth_segments(30000, seed=3, cn_max=CN_MAX)
 dev = BafGridDevice(**baf_args(seg))
 pl = S.r_seq(1, 7, 0.02)
 for nc in (8, 12, 16, 20, 24, 33, 40, 48):
