@@ -124,7 +124,7 @@ int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
  *   - the problem must fit: sqz_baf_grid_workspace_bytes(N_total, S, nP, ic1 - ic0) must
  *     be <= 16 MiB (16,777,216 bytes); larger problems are refused with SQZ_ERR_SIZE and
  *     a message naming both numbers.  BASELINE config 2 (3e4 segments, 91 x 61 grid)
- *     needs about 5.9 MiB;
+ *     needs about 6.4 MiB;
  *   - the first call on each device looks up the device address of the built-in scratch
  *     (one cudaGetSymbolAddress); make that first call before starting any stream
  *     capture on that device;

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Turns gpurun_out/ ncu artefacts into the tracked summaries under profiles/.
 
-    python tools/summarize_ncu.py <round-tag> <launches.csv> <full.ncu-rep> [<bench.json>...]
+    python tools/summarize_ncu.py <round-tag> <launches.csv>... <full.ncu-rep>... [<bench.json>...]
 """
 import collections
 import csv
@@ -9,34 +9,39 @@ import json
 import subprocess
 import sys
 
-tag, launches = sys.argv[1], sys.argv[2]
-reps = [a for a in sys.argv[3:] if a.endswith(".ncu-rep")]
-bench = [a for a in sys.argv[3:] if not a.endswith(".ncu-rep")]
+tag = sys.argv[1]
+lists = [a for a in sys.argv[2:] if a.endswith(".csv")]
+reps = [a for a in sys.argv[2:] if a.endswith(".ncu-rep")]
+bench = [a for a in sys.argv[2:] if a.endswith(".json")]
 out = []
-rows = [r for r in csv.reader(open(launches)) if len(r) > 5]
-hdr = rows[0]
-ik, iv, ig, ib = (hdr.index(c) for c in ("Kernel Name", "Metric Value", "Grid Size", "Block Size"))
-agg = collections.OrderedDict()
-for r in rows[1:]:
-    k = r[ik].split("(")[0]
-    agg.setdefault(k, {"ns": [], "grid": r[ig], "block": r[ib]})["ns"].append(
-        float(r[iv].replace(",", "")))
-tot = sum(sum(v["ns"]) for v in agg.values())
-out.append("# ncu launch list (%s)\n" % tag)
-out.append("Command: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv "
-           "python bench.py --steps 20 --warmup 3` (after the same command exited 0 without "
-           "ncu).  Times are cold-cache and serialised: compare shares, not absolutes.\n")
-out.append("| kernel | launches | grid | block | total ms | avg us | share |")
-out.append("|---|---|---|---|---|---|---|")
-for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1]["ns"])):
-    s = sum(v["ns"])
-    out.append("| `%s` | %d | %s | %s | %.3f | %.1f | %.1f%% |" % (
-        k, len(v["ns"]), v["grid"], v["block"], s / 1e6, s / len(v["ns"]) / 1e3, 100 * s / tot))
-step = [k for k in agg if "baf_" in k]
-stot = sum(sum(agg[k]["ns"]) for k in step)
-out.append("\nShare of the fit step (the four `baf_*` kernels only):\n")
-for k in step:
-    out.append("- `%s`: %.2f%%" % (k, 100 * sum(agg[k]["ns"]) / stot))
+for launches in lists:
+    rows = [r for r in csv.reader(open(launches)) if len(r) > 5]
+    hdr = rows[0]
+    ik, iv, ig, ib = (hdr.index(c) for c in ("Kernel Name", "Metric Value", "Grid Size", "Block Size"))
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        k = r[ik].split("(")[0]
+        agg.setdefault(k, {"ns": [], "grid": r[ig], "block": r[ib]})["ns"].append(
+            float(r[iv].replace(",", "")))
+    tot = sum(sum(v["ns"]) for v in agg.values())
+    c3 = "c3" in launches.split("/")[-1] or "config3" in launches
+    out.append("# ncu launch list (%s, %s)\n" % (tag, "config 3" if c3 else "config 2, the default workload"))
+    out.append("Command: `ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv "
+               "python bench.py %s` (after the same command exited 0 without "
+               "ncu).  Times are cold-cache and serialised: compare shares, not absolutes.\n"
+               % ("--steps 5 --warmup 3 --workload config3" if c3 else "--steps 20 --warmup 3"))
+    out.append("| kernel | launches | grid | block | total ms | avg us | share |")
+    out.append("|---|---|---|---|---|---|---|")
+    for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1]["ns"])):
+        s_ = sum(v["ns"])
+        out.append("| `%s` | %d | %s | %s | %.3f | %.1f | %.1f%% |" % (
+            k, len(v["ns"]), v["grid"], v["block"], s_ / 1e6, s_ / len(v["ns"]) / 1e3, 100 * s_ / tot))
+    step = [k for k in agg if "baf_" in k]
+    stot = sum(sum(agg[k]["ns"]) for k in step)
+    out.append("\nShare of the fit step (the `baf_*` kernels only):\n")
+    for k in step:
+        out.append("- `%s`: %.2f%%" % (k, 100 * sum(agg[k]["ns"]) / stot))
+    out.append("")
 
 for rep_ in reps:
     raw = subprocess.run(["ncu", "-i", rep_, "--page", "raw", "--csv"], capture_output=True,
