@@ -784,12 +784,12 @@ size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP
   if (n_copy_numbers < 1 || n_copy_numbers > kMaxCN || nCs < 1) return base;
   const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
   size_t cols = (size_t)nCs;
-  if (baf_colwarp_supported(n_copy_numbers, false)) {
-    // whichever kernel the call ends up with runs all columns in one batch: the
-    // segment-per-lane kernels keep 16 bytes per (column, copy number, segment), the
-    // column-per-lane kernel 8, in whole 32-column groups
+  if (colwarp_tile(n_copy_numbers, false, N_total, S, nP, nCs)) {
+    // the column-per-lane kernel would take this fit: 8 bytes per (column, copy number,
+    // segment) in whole 32-column groups.  (A call that cannot use it after all --
+    // ratio.priority, unsorted ploidies -- runs the split kernel in two batches.)
     size_t want = ((cols + 31) / 32) * baf_colwarp_group_bytes(n_copy_numbers, N_total);
-    if (want < cols * per_col) want = cols * per_col;
+    if (want < per_col) want = per_col;
     if (cap_bytes > 0 && want > cap_bytes) want = cap_bytes;
     return base + align256(want);
   }
