@@ -85,10 +85,13 @@ int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
  * at least sqz_baf_grid_workspace_bytes(...) bytes, 256-byte aligned. */
 size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard);
 /* The minimum above selects the fused kernel.  With more room the library runs the faster
- * split form (a per-column pre-pass whose output, 16 * n_copy_numbers * N_total bytes per
- * cellularity column, is streamed back by the grid kernel; columns are processed in
- * batches that fit).  This returns minimum + as many columns as fit under cap_bytes
- * (0 = no cap; at least one column).  n_copy_numbers = CNt_max - CNt_min + 1. */
+ * split forms: a per-column pre-pass whose output is streamed back by the grid kernel, 16 *
+ * n_copy_numbers * N_total bytes per cellularity column, or 8 * n_copy_numbers * N_total
+ * per column in whole groups of 32 columns for the kernel that large fits with CNt 0..7 or
+ * 0..20 get (one cellularity per lane); columns are processed in batches that fit.  This
+ * returns minimum + room for all columns of the kernel the planner will pick, at most
+ * cap_bytes of it (0 = no cap; at least one column).  The host entry points use a cap of
+ * 16 GiB.  n_copy_numbers = CNt_max - CNt_min + 1. */
 size_t sqz_baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP,
                                               int64_t nC_shard, int n_copy_numbers,
                                               size_t cap_bytes);
