@@ -203,7 +203,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 #pragma unroll 1
     for (int sg = 0; sg < nsg; ++sg) {
       const double2 rk = rkS[s * kSegB + sg];
-      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // sqrt(wub) [c * 32]
+      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // stored value of c: [c * 32]
 
       // (a) lower bound of every copy number over the tile (high words are enough: Qmax
       // below has a zero low word); argmin on the high words with the index packed in.

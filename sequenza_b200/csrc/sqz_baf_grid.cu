@@ -833,17 +833,15 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
     if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
   }
-  int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
+  const int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
   GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune != 0);
   // pre-pass scratch behind the fixed part of the workspace
   char* cw_buf = (char*)workspace + w.bytes;
   const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
   const int cw_pt = (mono_up || mono_dn) && env_int("SQZ_PRUNE", 1) != 0
                         ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
-  if (cw_pt && cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total)) {
+  if (cw_pt && cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total))
     g = plan_colwarp(N_total, S, nP, cw_pt);  // column-per-lane kernel: room for >= 32 columns
-    prune = 2;
-  }
   BafGridArgs a;
   a.S = S;
   a.seg_off = d_seg_off;
@@ -892,16 +890,16 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   // Split path when the workspace has room for at least one column of pre-pass output
   // (sqz_baf_grid_workspace_preferred_bytes); fused kernel otherwise.
   const bool use_split = env_int("SQZ_SPLIT", 1) != 0 && N_total > 0 &&
-                         (prune == 2 || baf_split_supported(m.nc, g.PT, g.threads)) &&
+                         (g.colwarp || baf_split_supported(m.nc, g.PT, g.threads)) &&
                          cw_bytes >= baf_split_column_bytes(m.nc, N_total);
   if (use_split) {
     if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
-    rc = prune == 2 ? baf_colwarp_run(a, m, g.PT, N_total, cw_buf, cw_bytes, w.partM, w.partE,
+    rc = g.colwarp ? baf_colwarp_run(a, m, g.PT, N_total, cw_buf, cw_bytes, w.partM, w.partE,
                                       st, prof ? w.stats : nullptr)
                     : baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
-                                    w.partE, st, prune, prof ? w.stats : nullptr);
+                                    w.partE, st, prune != 0, prof ? w.stats : nullptr);
     if (prof) {
-      prof->path = prune == 2 ? 3 : (prune ? 2 : 1);
+      prof->path = g.colwarp ? 3 : (prune ? 2 : 1);
       SQZ_CUDA(cudaMemcpyAsync(&prof->n_eval, w.stats, sizeof(unsigned long long),
                                cudaMemcpyDeviceToHost, st));
     }

@@ -27,7 +27,7 @@ size_t baf_split_column_bytes(int nc, int64_t N_total);
 bool baf_split_supported(int nc, int PT, int threads);
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, int prune, unsigned long long* stats);
+                  cudaStream_t st, bool prune, unsigned long long* stats);
 
 // Pruned grid kernel with one cellularity column per lane (sqz_baf_colwarp.cu), with its
 // own pre-pass and scratch layout: baf_colwarp_group_bytes per group of 32 columns.

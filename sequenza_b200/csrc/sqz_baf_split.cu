@@ -553,9 +553,8 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
 // Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
-                  cudaStream_t st, int prune, unsigned long long* stats) {
-  if (prune == 2) prune = 1;  // the column-per-lane kernel is driven by baf_colwarp_run
-  if (prune == 1 && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = 0;
+                  cudaStream_t st, bool prune, unsigned long long* stats) {
+  if (prune && (a.rp || pruned_smem_bytes(m.nc, PT, threads) > 200 * 1024)) prune = false;
   const size_t per_col = baf_split_column_bytes(m.nc, N_total);
   int64_t nCb_max = (int64_t)(cw_bytes / per_col);
   if (nCb_max < 1) return fail(SQZ_ERR_SIZE, "split path needs room for one column");
