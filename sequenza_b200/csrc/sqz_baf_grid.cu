@@ -638,7 +638,12 @@ static int colwarp_tile(int nc, bool rp, int64_t N_total, int64_t S, int64_t nP,
   if (nc > 8)  // CNt 0..20: a coarse ploidy axis keeps 4-6 copy numbers alive per warp and
                // the plain split kernel is as fast (91 x 61 grid: 1.44 vs 1.50 ms)
     return (nP >= 200 && u16 >= 2 * slots) ? 16 : 0;
-  if (nP > 96 && u32 >= 6 * slots) return 32;
+  // 32-wide tiles need fewer instructions per evaluation; 16-wide ones give twice the units
+  // and a cheaper per-chunk prologue.  Measured (tools/colwarp_vs_pruned.py,
+  // tools/shard_tile_width.py): 32 wins from 6 waves of units on, and from 2 waves on when
+  // the chunks are long (config 3 shards: 5.45 vs 7.01 ms at 113 columns).
+  const int64_t per_chunk = (S > 0 ? (N_total + S - 1) / S : 0) / ch;
+  if (nP > 96 && (u32 >= 6 * slots || (u32 >= 2 * slots && per_chunk >= 1000))) return 32;
   if (u16 >= 3 * slots) return 16;
   return 0;
 }

@@ -31,9 +31,11 @@ def test_config3_takes_the_column_per_lane_kernel():
     # one warp per CTA, 32-wide tiles, chunk count from the segment table alone
     p = plan(100000, 1, 601, 901, 7)
     assert (p["PT"], p["nPT"], p["threads"], p["chunks"], p["T"]) == (32, 19, 32, 64, 20)
-    # an eighth of the columns: fewer one-warp units, so 16-wide tiles; same chunks
+    # an eighth of the columns: four waves of one-warp units with long chunks keep the
+    # 32-wide tiles; the same grid over 3,000 segments (65 per chunk) takes 16-wide ones
     q = plan(100000, 1, 601, 113, 7)
-    assert (q["PT"], q["threads"], q["chunks"]) == (16, 32, 64)
+    assert (q["PT"], q["threads"], q["chunks"]) == (32, 32, 64)
+    assert plan(3000, 1, 601, 181, 7)["PT"] == 16 and plan(3000, 1, 601, 181, 7)["threads"] == 32
     # a shard too narrow to fill the lanes of a 32-column group stays segment-per-lane
     assert plan(100000, 1, 601, 12, 7)["threads"] == 128
     # ratio.priority has no column-per-lane instantiation

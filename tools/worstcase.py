@@ -1,6 +1,5 @@
 """Pruned vs split kernel over sd scales and grid resolutions (CNt 0..7)."""
 import os, sys
-import numpy as np
 sys.path.insert(0, ".")
 import torch
 import sequenza_b200 as S
