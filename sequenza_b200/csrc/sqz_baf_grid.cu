@@ -486,7 +486,7 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 // has synchronised.  Off by default; bench.py turns it on for the roofline numbers.
 struct ProfSet {
   cudaEvent_t ev[4];
-  int path = 0;                    // 0 fused, 1 split, 2 split + candidate pruning
+  int path = 0;                    // 0 fused, 1 split, 2 pruned (segment lanes), 3 pruned (column lanes)
   unsigned long long n_eval = 0;   // (segment, tile, copy number) evaluations, pruned path
 };
 static bool g_prof_on = false;
