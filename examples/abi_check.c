@@ -23,7 +23,10 @@ int main(void) {
       (fn_t)sqz_fit_finish_dev, (fn_t)sqz_model_points,
       (fn_t)sqz_fp64_peak, (fn_t)sqz_baf_grid_plan,
       (fn_t)sqz_profile_enable, (fn_t)sqz_profile_collect,
-      (fn_t)sqz_profile_counters};
+      (fn_t)sqz_profile_counters, (fn_t)sqz_baf_grid_units_workspace_bytes,
+      (fn_t)sqz_baf_grid_dev_units, (fn_t)sqz_peer_data_offset,
+      (fn_t)sqz_peer_alloc, (fn_t)sqz_peer_open, (fn_t)sqz_peer_close,
+      (fn_t)sqz_peer_free, (fn_t)sqz_peer_signal, (fn_t)sqz_peer_wait};
   printf("%s: %d entry points, %d device(s)\n", sqz_version(),
          (int)(sizeof syms / sizeof syms[0]), sqz_device_count());
   {

@@ -85,16 +85,17 @@ int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
  * at least sqz_baf_grid_workspace_bytes(...) bytes, 256-byte aligned. */
 size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard);
 /* The minimum above selects the fused kernel.  With more room the library runs the faster
- * split forms: a per-column pre-pass whose output is streamed back by the grid kernel, 16 *
- * n_copy_numbers * N_total bytes per cellularity column, or 8 * n_copy_numbers * N_total
- * per column in whole groups of 32 columns for the kernel that large fits with CNt 0..7 or
- * 0..20 get (one cellularity per lane); columns are processed in batches that fit.  This
- * returns minimum + room for all columns of the kernel the planner will pick, at most
- * cap_bytes of it (0 = no cap; at least one column).  The host entry points use a cap of
- * 16 GiB.  n_copy_numbers = CNt_max - CNt_min + 1. */
+ * split forms: a per-column pre-pass whose output is streamed back by the grid kernel, 8 *
+ * n_copy_numbers * N_total bytes per cellularity column, in whole groups of 32 columns for
+ * the kernel that large fits with CNt 0..7 or 0..20 get (one cellularity per lane); columns
+ * are processed in batches that fit.  This returns minimum + room for all nC_shard columns
+ * of the kernel the planner picks for the WHOLE grid of nC columns (the kernel, its tile
+ * width and its segment chunks never depend on the shard, so that a grid point gets the
+ * same bits from any shard), at most cap_bytes of it (0 = no cap; at least one column).
+ * The host entry points use a cap of 16 GiB.  n_copy_numbers = CNt_max - CNt_min + 1. */
 size_t sqz_baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP,
-                                              int64_t nC_shard, int n_copy_numbers,
-                                              size_t cap_bytes);
+                                              int64_t nC, int64_t nC_shard,
+                                              int n_copy_numbers, size_t cap_bytes);
 int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
                      const double* d_Bf, const double* d_depth_ratio,
                      const double* d_sd_Bf, const double* d_sd_ratio,
@@ -105,6 +106,56 @@ int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
                      const double* prior_value, int n_prior, int ratio_priority, int mode,
                      void* workspace, size_t workspace_bytes, void* stream,
                      double* d_lpp_sum_out);
+
+/* B1 sharded by UNITS instead of whole columns, for an even split of the grid over GPUs
+ * (the loop being split is still fit.cp over expand.grid, R/bayes.R:106-115).  The grid is
+ * cut into units of W columns x PT ploidies counted from its origin, unit = group * nPT +
+ * tile; sqz_baf_grid_plan reports W, PT, nPT and the unit count of the whole grid.  This
+ * call evaluates units u0 <= u < u1 and writes every result at its FINAL place of a
+ * whole-grid buffer (S x nC*nP doubles, ploidy fastest) -- of each of the n_out buffers in
+ * d_outs (a HOST array of device pointers): the caller's own buffer and, for a multi-GPU
+ * fit, the peers' buffers mapped into this process (peer access or CUDA IPC), so that the
+ * last kernel of the fit is also its all-gather over NVLink.  Grid points outside the
+ * unit range are not touched.  The caller orders the peers' reads after this call
+ * (sqz_peer_signal / sqz_peer_wait or a stream/host synchronisation).
+ * Workspace: sqz_baf_grid_units_workspace_bytes(...) (cap_bytes as above). */
+size_t sqz_baf_grid_units_workspace_bytes(int64_t N_total, int64_t S, const double* ploidy,
+                                          int64_t nP, int64_t nC, int CNt_min, int CNt_max,
+                                          int CNn, int ratio_priority, int64_t u0, int64_t u1,
+                                          size_t cap_bytes);
+int sqz_baf_grid_dev_units(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
+                           const double* d_Bf, const double* d_depth_ratio,
+                           const double* d_sd_Bf, const double* d_sd_ratio,
+                           const double* d_weight_Bf, const double* d_weight_ratio,
+                           const double* ploidy, int64_t nP, const double* cellularity,
+                           int64_t nC, int64_t u0, int64_t u1,
+                           const double* d_avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                           const double* prior_CN, const double* prior_value, int n_prior,
+                           int ratio_priority, int mode, void* workspace,
+                           size_t workspace_bytes, void* stream, double* const* d_outs,
+                           int n_out);
+
+/* Result buffers shared by the GPUs of one box, one process per GPU -- the assembly of
+ * result$LPP that the reference gets from its mclapply workers over pipes
+ * (R/bayes.R:114-116).  A peer buffer is sqz_peer_data_offset() bytes of header (one
+ * 8-byte flag per rank) followed by data_bytes of data.  sqz_peer_alloc creates one on the
+ * current device and exports its 64-byte CUDA IPC handle; the other processes map it with
+ * sqz_peer_open (addresses valid in the opening process; NVLink peer mapping) and pass
+ * `base + sqz_peer_data_offset()` of every rank to sqz_baf_grid_dev_units as d_outs.
+ * After the fit, on the same stream: sqz_peer_signal (all earlier stores of this GPU made
+ * visible, then flag[my_rank] = epoch in every buffer of d_bases, a host array of the n
+ * ranks' bases in rank order) and sqz_peer_wait (until all n flags of the own buffer show
+ * at least epoch; a peer missing for 10 s traps the kernel).  Epochs must grow from call
+ * to call; alternate between two data areas so that nobody overwrites what a slower rank
+ * still reads.  At most 16 ranks. */
+size_t sqz_peer_data_offset(void);
+int sqz_peer_alloc(size_t data_bytes, void** d_base, unsigned char* handle64,
+                   size_t* total_bytes);
+int sqz_peer_open(const unsigned char* handle64, void** d_base);
+int sqz_peer_close(void* d_base);
+int sqz_peer_free(void* d_base);
+int sqz_peer_signal(void* const* d_bases, int n, int my_rank, uint64_t epoch, void* stream);
+int sqz_peer_wait(void* d_base, int n, uint64_t epoch, void* stream);
 
 /* ---------------------------------------------------------------------------------
  * Grid fit for callers that cannot allocate device memory.  This entry point has no
@@ -269,11 +320,15 @@ int sqz_model_points(int kind, double cellularity, double ploidy, double avg_dep
  * --------------------------------------------------------------------------------- */
 int sqz_fp64_peak(int device, int repeats, double* tflops_out);
 
-/* Launch geometry the fast grid path would use, for reporting: out5 = ploidies per CTA
- * tile, tiles per column, segment chunks, threads per CTA, number of (CNt, B) types.
- * No counterpart in the reference. */
-int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, int CNt_min,
-                      int CNt_max, int CNn, int ratio_priority, int* out5);
+/* Launch geometry of the fast grid path for a grid of nC x nP points, for reporting and for
+ * sharding by units: out8 = ploidies per tile (PT), tiles per column (nPT), segment chunks,
+ * threads per CTA, number of (CNt, B) types, kernel family (0 fused, 1 split, 2 pruned with
+ * one segment per lane, 3 pruned with one cellularity column per lane -- what the preferred
+ * workspace gives), columns per unit (W), units of the whole grid (ceil(nC / W) * nPT).
+ * `ploidy` (nP host values, or NULL = sorted) matters because candidate pruning needs a
+ * monotone ploidy axis.  No counterpart in the reference. */
+int sqz_baf_grid_plan(int64_t N_total, int64_t S, const double* ploidy, int64_t nP, int64_t nC,
+                      int CNt_min, int CNt_max, int CNn, int ratio_priority, int64_t* out8);
 
 /* Per-kernel timing of fast-mode grid calls on the current device: after
  * sqz_profile_enable(1), every sqz_baf_grid_dev / sqz_baf_grid call records CUDA events
@@ -287,7 +342,8 @@ int sqz_profile_collect(double* ms3, int* n_calls);
  * one cellularity column per lane); *n_eval = (segment, ploidy tile, copy number)
  * evaluations the pruned kernel actually made, summed over the recorded calls (path 3:
  * per column, counting what the column's warp executed). */
-int sqz_profile_counters(int* path, unsigned long long* n_eval);
+/* *launches = kernels the recorded calls launched (counted at the launch sites). */
+int sqz_profile_counters(int* path, unsigned long long* n_eval, long long* launches);
 
 #ifdef __cplusplus
 }

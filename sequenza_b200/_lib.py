@@ -30,11 +30,23 @@ SIGNATURES = {
     "sqz_baf_grid_batch": (_i, [_i64, _p] + [_p] * 6 + [_p, _i64, _p, _i64, _p, _i, _i, _i,
                                 _p, _p, _i, _i, _i, _i, _p]),
     "sqz_baf_grid_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64]),
-    "sqz_baf_grid_workspace_preferred_bytes": (_sz, [_i64, _i64, _i64, _i64, _i, _sz]),
+    "sqz_baf_grid_workspace_preferred_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i, _sz]),
+    "sqz_baf_grid_units_workspace_bytes": (_sz, [_i64, _i64, _p, _i64, _i64, _i, _i, _i, _i,
+                                                 _i64, _i64, _sz]),
+    "sqz_baf_grid_dev_units": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64,
+                                    _i64, _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _sz, _p, _p,
+                                    _i]),
     "sqz_baf_grid_dev": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64, _i64,
                               _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _sz, _p, _p]),
     "sqz_baf_grid_dev_noalloc": (_i, [_i64, _p, _i64] + [_p] * 6 + [_p, _i64, _p, _i64, _i64,
                                       _i64, _p, _i, _i, _i, _p, _p, _i, _i, _i, _p, _p]),
+    "sqz_peer_data_offset": (_sz, []),
+    "sqz_peer_alloc": (_i, [_sz, _p, _p, _p]),
+    "sqz_peer_open": (_i, [_p, _p]),
+    "sqz_peer_close": (_i, [_p]),
+    "sqz_peer_free": (_i, [_p]),
+    "sqz_peer_signal": (_i, [_p, _i, _i, C.c_uint64, _p]),
+    "sqz_peer_wait": (_i, [_p, _i, C.c_uint64, _p]),
     "sqz_baf_point": (_i, [_p] * 6 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _i, _p]),
     "sqz_baf_point_dev": (_i, [_p] * 6 + [_i64, _d, _d, _d, _i, _i, _i, _p, _p, _i, _i, _p,
                                _p]),
@@ -55,10 +67,10 @@ SIGNATURES = {
     "sqz_fit_finish_dev": (_i, [_p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "sqz_model_points": (_i, [_i, _d, _d, _d, _i, _i, _i, _p, _p, _i, _p, _p]),
     "sqz_fp64_peak": (_i, [_i, _i, _p]),
-    "sqz_baf_grid_plan": (_i, [_i64, _i64, _i64, _i64, _i, _i, _i, _i, _p]),
+    "sqz_baf_grid_plan": (_i, [_i64, _i64, _p, _i64, _i64, _i, _i, _i, _i, _p]),
     "sqz_profile_enable": (_i, [_i]),
     "sqz_profile_collect": (_i, [_p, _p]),
-    "sqz_profile_counters": (_i, [_p, _p]),
+    "sqz_profile_counters": (_i, [_p, _p, _p]),
 }
 
 _lib = None

@@ -6,6 +6,7 @@
 // R process).  The _dev entry points are thin argument checks over the launchers.
 #include <algorithm>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "sqz_common.cuh"
@@ -21,8 +22,21 @@ int fail(int code, const std::string& msg) {
 
 // launchers (sqz_baf_grid.cu, sqz_mufreq.cu)
 size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs);
-size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
-                                          int n_copy_numbers, size_t cap_bytes);
+size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC,
+                                          int64_t nCs, int n_copy_numbers, size_t cap_bytes);
+size_t baf_grid_units_workspace_bytes(int64_t N_total, int64_t S, const double* h_ploidy,
+                                      int64_t nP, int64_t nC, int CNt_min, int CNt_max, int CNn,
+                                      int ratio_priority, int64_t u0, int64_t u1,
+                                      size_t cap_bytes);
+int baf_grid_launch_units(int64_t S, const int64_t* d_seg_off, int64_t N_total,
+                          const double* d_Bf, const double* d_ratio, const double* d_sdBf,
+                          const double* d_sdr, const double* d_wBf, const double* d_wr,
+                          const double* h_ploidy, int64_t nP, const double* h_cell, int64_t nC,
+                          int64_t u0, int64_t u1, const double* d_adr, int CNt_min,
+                          int CNt_max, int CNn, const double* prior_CN,
+                          const double* prior_value, int n_prior, int ratio_priority, int mode,
+                          void* workspace, size_t workspace_bytes, cudaStream_t st,
+                          double* const* d_outs, int n_out);
 int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
                     const double* d_ratio, const double* d_sdBf, const double* d_sdr,
                     const double* d_wBf, const double* d_wr, const double* h_ploidy,
@@ -30,17 +44,17 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
                     const double* d_adr, int CNt_min, int CNt_max, int CNn,
                     const double* prior_CN, const double* prior_value, int n_prior,
                     int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
-                    cudaStream_t st, double* d_out);
+                    cudaStream_t st, double* d_out, bool allow_profile = true);
 int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_sdBf,
                      const double* d_sdr, const double* d_wBf, const double* d_wr, int64_t N,
                      double cellularity, double ploidy, double adr, int CNt_min, int CNt_max,
                      int CNn, const double* prior_CN, const double* prior_value, int n_prior,
                      int ratio_priority, cudaStream_t st, double* d_out);
-int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_min, int CNt_max,
-                  int CNn, int ratio_priority, int* out5);
+int baf_grid_plan(int64_t N_total, int64_t S, const double* h_ploidy, int64_t nP, int64_t nC,
+                  int CNt_min, int CNt_max, int CNn, int ratio_priority, int64_t* out8);
 int profile_enable(int on);
 int profile_collect(double* ms3, int* n_calls);
-int profile_counters(int* path, unsigned long long* n_eval);
+int profile_counters(int* path, unsigned long long* n_eval, long long* launches);
 size_t mufreq_grid_workspace_bytes(int64_t N, int64_t nP, int64_t nCs);
 int mufreq_point_launch(const double* d_F, const double* d_ratio, const double* d_wm,
                         const double* d_wr, int64_t N, double cellularity, double ploidy,
@@ -71,12 +85,14 @@ int model_points_launch(int kind, double cellularity, double ploidy, double adr,
 struct DevCtx {
   bool live = false;
   cudaStream_t st = nullptr;
+  cudaEvent_t ev_in = nullptr, ev_done = nullptr;  // inputs staged / work finished
   void* in = nullptr;   // staged inputs
   size_t in_cap = 0;
   void* ws = nullptr;   // kernel workspace
   size_t ws_cap = 0;
   void* out = nullptr;  // result slice
   size_t out_cap = 0;
+  unsigned long long peers = 0;  // devices whose memory this device may address
 };
 static std::mutex g_mu;
 static std::vector<DevCtx> g_ctx;
@@ -86,10 +102,38 @@ static int grow(void** p, size_t* cap, size_t need) {
   if (*p) SQZ_CUDA(cudaFree(*p));
   *p = nullptr;
   *cap = 0;
-  size_t want = need + need / 4 + 256;
+  // a little headroom for small buffers that creep up; none for multi-GiB requests
+  size_t want = need + (need < ((size_t)256 << 20) ? need / 4 : 0) + 256;
   SQZ_CUDA(cudaMalloc(p, want));
   *cap = want;
   return SQZ_OK;
+}
+
+// Workspace of a grid fit: the preferred size if the device has it, else halved towards
+// the minimum (fewer pre-pass columns per batch; the results do not depend on it).
+static int grow_ws(DevCtx* c, size_t need_min, size_t need_pref, size_t* got) {
+  size_t want = need_pref > need_min ? need_pref : need_min;
+  if (want <= c->ws_cap) {
+    *got = want;
+    return SQZ_OK;
+  }
+  for (;;) {
+    if (c->ws) cudaFree(c->ws);
+    c->ws = nullptr;
+    c->ws_cap = 0;
+    cudaError_t e = cudaMalloc(&c->ws, want + 256);
+    if (e == cudaSuccess) {
+      c->ws_cap = want + 256;
+      *got = want;
+      return SQZ_OK;
+    }
+    cudaGetLastError();  // out of memory: clear it and ask for less
+    if (e != cudaErrorMemoryAllocation || want == need_min)
+      return fail(SQZ_ERR_CUDA, std::string("cudaMalloc of the grid workspace failed: ") +
+                                    cudaGetErrorString(e));
+    want = need_min + (want - need_min) / 2;
+    if (want - need_min < ((size_t)1 << 20)) want = need_min;
+  }
 }
 
 static int ctx_for(int dev, DevCtx** out) {
@@ -98,10 +142,33 @@ static int ctx_for(int dev, DevCtx** out) {
   SQZ_CUDA(cudaSetDevice(dev));
   if (!c.live) {
     SQZ_CUDA(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+    SQZ_CUDA(cudaEventCreateWithFlags(&c.ev_in, cudaEventDisableTiming));
+    SQZ_CUDA(cudaEventCreateWithFlags(&c.ev_done, cudaEventDisableTiming));
     c.live = true;
   }
   *out = &c;
   return SQZ_OK;
+}
+
+// may device `dev` (current) address memory of device `peer`?  Enabled on first use.
+static bool peer_ok(int dev, int peer) {
+  if (dev == peer) return true;
+  if (dev >= 64 || peer >= 64) return false;
+  DevCtx& c = g_ctx[dev];
+  if (c.peers & (1ull << peer)) return true;
+  int can = 0;
+  if (cudaDeviceCanAccessPeer(&can, dev, peer) != cudaSuccess || !can) {
+    cudaGetLastError();
+    return false;
+  }
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return false;
+  }
+  cudaGetLastError();
+  c.peers |= 1ull << peer;
+  return true;
 }
 
 static int usable_devices(int n_gpus, int* ndev) {
@@ -125,6 +192,129 @@ struct DeviceGuard {
     if (prev >= 0) cudaSetDevice(prev);
   }
 };
+
+// wait for everything queued on the first ndev devices (also on error paths: nothing may
+// still be running on caller-visible buffers when a host entry point returns)
+static cudaError_t sync_devices(int ndev) {
+  cudaError_t first = cudaSuccess;
+  for (int d = 0; d < ndev && d < (int)g_ctx.size(); ++d) {
+    if (!g_ctx[d].live) continue;
+    cudaError_t e = cudaSetDevice(d);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(g_ctx[d].st);
+    if (e != cudaSuccess && first == cudaSuccess) first = e;
+    cudaGetLastError();
+  }
+  return first;
+}
+
+struct GridCall {  // arguments every device of a host grid call shares
+  int64_t S;
+  const int64_t* seg_off;
+  const double* const* vec;
+  const double* ploidy;
+  int64_t nP;
+  const double* cell;
+  int64_t nC;
+  const double* adr;
+  int CNt_min, CNt_max, CNn;
+  const double* prior_CN;
+  const double* prior_value;
+  int n_prior, ratio_priority, mode;
+};
+
+// One sample table, several devices: the grid is cut into units (sqz_baf_grid.cuh) and
+// every device writes its results straight into device 0's whole-grid buffer over NVLink
+// (peer access).  The segment table crosses PCIe once, to device 0, and reaches the other
+// devices by peer copies; each device is driven by its own host thread; the assembled
+// LPP vector leaves device 0 in one copy.
+static int baf_grid_host_units(const GridCall& g, int ndev, double* out) {
+  const int64_t N = g.seg_off[g.S], G = g.nP * g.nC;
+  int64_t plan[8];
+  int rc = baf_grid_plan(N, g.S, g.ploidy, g.nP, g.nC, g.CNt_min, g.CNt_max, g.CNn,
+                         g.ratio_priority, plan);
+  if (rc) return rc;
+  const int64_t n_units = plan[7];
+  if (ndev > n_units) ndev = (int)n_units;
+  const size_t vbytes = a256((size_t)(N > 0 ? N : 1) * 8);
+  const size_t off_b = a256((size_t)(g.S + 1) * 8), adr_b = a256((size_t)g.S * 8);
+  const size_t in_need = 6 * vbytes + off_b + adr_b;
+  for (int d = 0; d < ndev; ++d) {
+    DevCtx* c;
+    if ((rc = ctx_for(d, &c))) return rc;
+    if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
+  }
+  DevCtx* root = &g_ctx[0];
+  SQZ_CUDA(cudaSetDevice(0));
+  if ((rc = grow(&root->out, &root->out_cap, (size_t)(g.S * G) * 8))) return rc;
+  {  // host -> device 0, once
+    char* p = (char*)root->in;
+    for (int k = 0; k < 6; ++k, p += vbytes)
+      if (N > 0)
+        SQZ_CUDA(cudaMemcpyAsync(p, g.vec[k], (size_t)N * 8, cudaMemcpyHostToDevice, root->st));
+    SQZ_CUDA(cudaMemcpyAsync(p, g.seg_off, (size_t)(g.S + 1) * 8, cudaMemcpyHostToDevice, root->st));
+    SQZ_CUDA(cudaMemcpyAsync(p + off_b, g.adr, (size_t)g.S * 8, cudaMemcpyHostToDevice, root->st));
+    SQZ_CUDA(cudaEventRecord(root->ev_in, root->st));
+  }
+  std::vector<int> rcs(ndev, SQZ_OK);
+  std::vector<std::string> msgs(ndev);
+  auto run_dev = [&](int d) {
+    auto body = [&]() -> int {
+      DevCtx* c = &g_ctx[d];
+      SQZ_CUDA(cudaSetDevice(d));
+      if (d != 0) {
+        if (!peer_ok(d, 0)) return fail(SQZ_ERR_CUDA, "no peer access to device 0");
+        SQZ_CUDA(cudaStreamWaitEvent(c->st, root->ev_in, 0));
+        SQZ_CUDA(cudaMemcpyPeerAsync(c->in, d, root->in, 0, in_need, c->st));
+      }
+      const int64_t u0 = n_units * d / ndev, u1 = n_units * (d + 1) / ndev;
+      const size_t ws_min = baf_grid_units_workspace_bytes(N, g.S, g.ploidy, g.nP, g.nC, g.CNt_min,
+                                                           g.CNt_max, g.CNn, g.ratio_priority, u0,
+                                                           u1, 1);
+      const size_t ws_pref = baf_grid_units_workspace_bytes(N, g.S, g.ploidy, g.nP, g.nC,
+                                                            g.CNt_min, g.CNt_max, g.CNn,
+                                                            g.ratio_priority, u0, u1,
+                                                            (size_t)16 << 30);
+      size_t ws_got = 0;
+      int r = grow_ws(c, ws_min, ws_pref, &ws_got);
+      if (r) return r;
+      const char* p = (const char*)c->in;
+      const double* dv[6];
+      for (int k = 0; k < 6; ++k, p += vbytes) dv[k] = (const double*)p;
+      double* outs[1] = {(double*)root->out};
+      r = baf_grid_launch_units(g.S, (const int64_t*)p, N, dv[0], dv[1], dv[2], dv[3], dv[4],
+                                dv[5], g.ploidy, g.nP, g.cell, g.nC, u0, u1,
+                                (const double*)(p + off_b), g.CNt_min, g.CNt_max, g.CNn,
+                                g.prior_CN, g.prior_value, g.n_prior, g.ratio_priority, g.mode,
+                                c->ws, ws_got, c->st, outs, 1);
+      if (r) return r;
+      SQZ_CUDA(cudaEventRecord(c->ev_done, c->st));
+      return SQZ_OK;
+    };
+    rcs[d] = body();
+    if (rcs[d]) msgs[d] = g_err;
+  };
+  {
+    std::vector<std::thread> th;
+    for (int d = 1; d < ndev; ++d) th.emplace_back(run_dev, d);
+    run_dev(0);
+    for (auto& t : th) t.join();
+  }
+  for (int d = 0; d < ndev; ++d)
+    if (rcs[d]) {
+      sync_devices(ndev);
+      return fail(rcs[d], msgs[d]);
+    }
+  SQZ_CUDA(cudaSetDevice(0));
+  for (int d = 1; d < ndev; ++d) SQZ_CUDA(cudaStreamWaitEvent(root->st, g_ctx[d].ev_done, 0));
+  SQZ_CUDA(cudaMemcpyAsync(out, root->out, (size_t)(g.S * G) * 8, cudaMemcpyDeviceToHost,
+                           root->st));
+  cudaError_t e = cudaStreamSynchronize(root->st);
+  if (e != cudaSuccess) {
+    sync_devices(ndev);
+    return fail(SQZ_ERR_CUDA, std::string("grid fit failed: ") + cudaGetErrorString(e));
+  }
+  return SQZ_OK;
+}
 
 static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const vec[6],
                          const double* ploidy, int64_t nP, const double* cell, int64_t nC,
@@ -150,9 +340,23 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
   const int64_t G = nP * nC;
   // Shards.  A cohort (at least one sample per device) is cut by sample at
   // segment-balanced boundaries, so that each device receives only its own samples'
-  // segments; otherwise every device receives all segments and takes a contiguous block
-  // of cellularity columns.
+  // segments.  Otherwise every device works on all segments and the grid is cut into
+  // units (baf_grid_host_units) or, without peer access between the devices, into
+  // contiguous blocks of cellularity columns.
   const bool by_sample = ndev > 1 && S >= ndev;
+  if (!by_sample && ndev > 1) {
+    bool peers = true;
+    for (int d = 1; d < ndev && peers; ++d) {
+      DevCtx* c;
+      if ((rc = ctx_for(d, &c))) return rc;
+      peers = peer_ok(d, 0);
+    }
+    if (peers) {
+      GridCall g{S, seg_off, vec, ploidy, nP, cell, nC, adr, CNt_min, CNt_max, CNn,
+                 prior_CN, prior_value, n_prior, ratio_priority, mode};
+      return baf_grid_host_units(g, ndev, out);
+    }
+  }
   if (!by_sample && ndev > nC) ndev = (int)nC;
   std::vector<int64_t> c0(ndev + 1), s0(ndev + 1);
   for (int d = 0; d <= ndev; ++d) {
@@ -169,12 +373,12 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
   s0[0] = 0;
   s0[ndev] = S;
   std::vector<int64_t> off_local(by_sample ? S + ndev : 0);
-  for (int d = 0; d < ndev; ++d) {
+  auto queue_device = [&](int d) -> int {
     // device d: samples [sa, sb) x columns [ca, cb)
     const int64_t sa = by_sample ? s0[d] : 0, sb = by_sample ? s0[d + 1] : S;
     const int64_t ca = by_sample ? 0 : c0[d], cb = by_sample ? nC : c0[d + 1];
     const int64_t Sd = sb - sa, nCs = cb - ca;
-    if (Sd <= 0 || nCs <= 0) continue;
+    if (Sd <= 0 || nCs <= 0) return SQZ_OK;
     const int64_t n_lo = seg_off[sa], Nd = seg_off[sb] - n_lo;
     const int64_t* h_off = seg_off;
     if (by_sample) {
@@ -183,15 +387,18 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
       h_off = o;
     }
     DevCtx* c;
-    if ((rc = ctx_for(d, &c))) return rc;
+    int r;
+    if ((r = ctx_for(d, &c))) return r;
     const size_t vbytes = a256((size_t)(Nd > 0 ? Nd : 1) * 8);
     const size_t in_need = 6 * vbytes + a256((size_t)(Sd + 1) * 8) + a256((size_t)Sd * 8);
-    if ((rc = grow(&c->in, &c->in_cap, in_need))) return rc;
-    const size_t ws_need = baf_grid_workspace_preferred_bytes(Nd, Sd, nP, nCs,
-                                                              CNt_max - CNt_min + 1,
-                                                              (size_t)16 << 30);
-    if ((rc = grow(&c->ws, &c->ws_cap, ws_need))) return rc;
-    if ((rc = grow(&c->out, &c->out_cap, (size_t)(Sd * nCs * nP) * 8))) return rc;
+    if ((r = grow(&c->in, &c->in_cap, in_need))) return r;
+    const int ncn = CNt_max - CNt_min + 1;
+    size_t ws_got = 0;
+    if ((r = grow_ws(c, baf_grid_workspace_preferred_bytes(Nd, Sd, nP, nC, nCs, ncn, 1),
+                     baf_grid_workspace_preferred_bytes(Nd, Sd, nP, nC, nCs, ncn,
+                                                        (size_t)16 << 30), &ws_got)))
+      return r;
+    if ((r = grow(&c->out, &c->out_cap, (size_t)(Sd * nCs * nP) * 8))) return r;
     char* p = (char*)c->in;
     const double* dv[6];
     for (int k = 0; k < 6; ++k) {
@@ -205,31 +412,34 @@ static int baf_grid_host(int64_t S, const int64_t* seg_off, const double* const 
     p += a256((size_t)(Sd + 1) * 8);
     double* d_adr = (double*)p;
     SQZ_CUDA(cudaMemcpyAsync(d_adr, adr + sa, (size_t)Sd * 8, cudaMemcpyHostToDevice, c->st));
-    rc = baf_grid_launch(Sd, d_off, Nd, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], ploidy, nP,
-                         cell, nC, ca, cb, d_adr, CNt_min, CNt_max, CNn, prior_CN,
-                         prior_value, n_prior, ratio_priority, mode, c->ws, c->ws_cap, c->st,
-                         (double*)c->out);
-    if (rc) return rc;
-  }
-  // Results are copied only after every device has its work queued: a device-to-host
-  // copy into pageable memory blocks the calling thread until that device is done.
-  for (int d = 0; d < ndev; ++d) {
+    return baf_grid_launch(Sd, d_off, Nd, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5], ploidy, nP,
+                           cell, nC, ca, cb, d_adr, CNt_min, CNt_max, CNn, prior_CN,
+                           prior_value, n_prior, ratio_priority, mode, c->ws, ws_got, c->st,
+                           (double*)c->out);
+  };
+  auto read_back = [&](int d) -> int {
     const int64_t sa = by_sample ? s0[d] : 0, sb = by_sample ? s0[d + 1] : S;
     const int64_t ca = by_sample ? 0 : c0[d], cb = by_sample ? nC : c0[d + 1];
     const int64_t Sd = sb - sa, nCs = cb - ca;
-    if (Sd <= 0 || nCs <= 0) continue;
+    if (Sd <= 0 || nCs <= 0) return SQZ_OK;
     DevCtx* c = &g_ctx[d];
     SQZ_CUDA(cudaSetDevice(d));
     // device slice [Sd][nCs*nP] -> host rows sa.. of [S][G] at column offset ca*nP
     SQZ_CUDA(cudaMemcpy2DAsync(out + sa * G + ca * nP, (size_t)G * 8, c->out,
                                (size_t)(nCs * nP) * 8, (size_t)(nCs * nP) * 8, (size_t)Sd,
                                cudaMemcpyDeviceToHost, c->st));
-  }
-  for (int d = 0; d < ndev; ++d) {
-    if ((int)g_ctx.size() <= d || !g_ctx[d].live) continue;
-    SQZ_CUDA(cudaSetDevice(d));
-    SQZ_CUDA(cudaStreamSynchronize(g_ctx[d].st));
-  }
+    return SQZ_OK;
+  };
+  for (int d = 0; d < ndev && !rc; ++d) rc = queue_device(d);
+  // Results are copied only after every device has its work queued: a device-to-host
+  // copy into pageable memory blocks the calling thread until that device is done.
+  for (int d = 0; d < ndev && !rc; ++d) rc = read_back(d);
+  std::string msg = rc ? g_err : std::string();
+  // also after an error: nothing stays queued behind the caller's back
+  const cudaError_t e = sync_devices(ndev);
+  if (rc) return fail(rc, msg);
+  if (e != cudaSuccess)
+    return fail(SQZ_ERR_CUDA, std::string("grid fit failed: ") + cudaGetErrorString(e));
   return SQZ_OK;
 }
 
@@ -316,6 +526,8 @@ int sqz_release(void) {
     if (c.ws) cudaFree(c.ws);
     if (c.out) cudaFree(c.out);
     cudaStreamDestroy(c.st);
+    if (c.ev_in) cudaEventDestroy(c.ev_in);
+    if (c.ev_done) cudaEventDestroy(c.ev_done);
     c = DevCtx();
   }
   return SQZ_OK;
@@ -354,9 +566,38 @@ size_t sqz_baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int6
 }
 
 size_t sqz_baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP,
-                                              int64_t nC_shard, int n_copy_numbers,
-                                              size_t cap_bytes) {
-  return baf_grid_workspace_preferred_bytes(N_total, S, nP, nC_shard, n_copy_numbers, cap_bytes);
+                                              int64_t nC, int64_t nC_shard,
+                                              int n_copy_numbers, size_t cap_bytes) {
+  return baf_grid_workspace_preferred_bytes(N_total, S, nP, nC, nC_shard, n_copy_numbers,
+                                            cap_bytes);
+}
+
+size_t sqz_baf_grid_units_workspace_bytes(int64_t N_total, int64_t S, const double* ploidy,
+                                          int64_t nP, int64_t nC, int CNt_min, int CNt_max,
+                                          int CNn, int ratio_priority, int64_t u0, int64_t u1,
+                                          size_t cap_bytes) {
+  return baf_grid_units_workspace_bytes(N_total, S, ploidy, nP, nC, CNt_min, CNt_max, CNn,
+                                        ratio_priority, u0, u1, cap_bytes);
+}
+
+int sqz_baf_grid_dev_units(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
+                           const double* d_Bf, const double* d_depth_ratio,
+                           const double* d_sd_Bf, const double* d_sd_ratio,
+                           const double* d_weight_Bf, const double* d_weight_ratio,
+                           const double* ploidy, int64_t nP, const double* cellularity,
+                           int64_t nC, int64_t u0, int64_t u1,
+                           const double* d_avg_depth_ratio, int CNt_min, int CNt_max, int CNn,
+                           const double* prior_CN, const double* prior_value, int n_prior,
+                           int ratio_priority, int mode, void* workspace,
+                           size_t workspace_bytes, void* stream, double* const* d_outs,
+                           int n_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return baf_grid_launch_units(S, d_seg_offsets, N_total, d_Bf, d_depth_ratio, d_sd_Bf,
+                               d_sd_ratio, d_weight_Bf, d_weight_ratio, ploidy, nP, cellularity,
+                               nC, u0, u1, d_avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN,
+                               prior_value, n_prior, ratio_priority, mode, workspace,
+                               workspace_bytes, (cudaStream_t)stream, d_outs, n_out);
 }
 
 int sqz_baf_grid_dev(int64_t S, const int64_t* d_seg_offsets, int64_t N_total,
@@ -609,16 +850,16 @@ int sqz_model_points(int kind, double cellularity, double ploidy, double avg_dep
                              CNn, prior_CN, prior_value, n_prior, T_out, out);
 }
 
-int sqz_baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nC_shard, int CNt_min,
-                      int CNt_max, int CNn, int ratio_priority, int* out5) {
-  if (!out5) return fail(SQZ_ERR_ARG, "out5 is null");
-  return baf_grid_plan(N_total, S, nP, nC_shard, CNt_min, CNt_max, CNn, ratio_priority, out5);
+int sqz_baf_grid_plan(int64_t N_total, int64_t S, const double* ploidy, int64_t nP, int64_t nC,
+                      int CNt_min, int CNt_max, int CNn, int ratio_priority, int64_t* out8) {
+  if (!out8) return fail(SQZ_ERR_ARG, "out8 is null");
+  return baf_grid_plan(N_total, S, ploidy, nP, nC, CNt_min, CNt_max, CNn, ratio_priority, out8);
 }
 
 int sqz_profile_enable(int on) { return profile_enable(on); }
 int sqz_profile_collect(double* ms3, int* n_calls) { return profile_collect(ms3, n_calls); }
-int sqz_profile_counters(int* path, unsigned long long* n_eval) {
-  return profile_counters(path, n_eval);
+int sqz_profile_counters(int* path, unsigned long long* n_eval, long long* launches) {
+  return profile_counters(path, n_eval, launches);
 }
 
 int sqz_fp64_peak(int device, int repeats, double* tflops_out) {

@@ -103,7 +103,7 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
 template <int PT, int NC>
 __global__ void __launch_bounds__(32, 8)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
-                        int nCb, int nCG, int64_t N_total, double* __restrict__ partM,
+                        int nCb, int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
                         long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int kSegDoubles = NC * 32;  // one segment of a column group
   constexpr int kSegB = NC <= 8 ? 2 : 1;  // segments per stage (a stage is at most 5.25 KB)
@@ -118,13 +118,14 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   int* Ec = reinterpret_cast<int*>(qS + PT * 32);                                   // [PT][32]
   __shared__ __align__(8) unsigned long long full[kRing];
 
+  // CTA -> (unit of this launch, chunk, sample); units run tile-fastest inside a column
+  // group, so the tiles of one (group, chunk) are neighbours in the grid and share L2 rows
   int64_t b = blockIdx.x;
-  const int tile = (int)(b % a.nPT);
-  b /= a.nPT;
-  const int cg = (int)(b % nCG);
-  b /= nCG;
+  const int ub = ub0 + (int)(b % nUb);  // unit, counted from the first group of this batch
+  b /= nUb;
   const int chunk = (int)(b % a.nChunk);
   const int64_t smp = b / a.nChunk;
+  const int cg = ub / a.nPT, tile = ub - cg * a.nPT;
 
   if (lane == 0) {
     for (int s = 0; s < kRing; ++s) mbar_init(&full[s], 1);
@@ -343,8 +344,18 @@ static size_t colwarp_smem_bytes(int NC, int PT) {
          (size_t)PT * 32 * sizeof(int);
 }
 
-// CNt 0..7 (sequenza.fit, R/bayes.R:40) and CNt 0..20 (sequenza.results, R/analysis.R)
-bool baf_colwarp_supported(int nc, bool rp) { return (nc == 8 || nc == 21) && !rp; }
+static size_t colterm_cg_smem_bytes(int nc, int T) {
+  return (size_t)(T + 2 * nc) * 32 * sizeof(double);
+}
+
+// CNt 0..7 (sequenza.fit, R/bayes.R:40) and CNt 0..20 (sequenza.results, R/results.R:128).
+// The pre-pass keeps the model BAF of 32 columns in shared memory: a shifted range with
+// many rows per copy number (e.g. CNt 3..23) would not fit the default 48 KB and takes the
+// split kernel instead.
+bool baf_colwarp_supported(int nc, int CNt_min, int T, bool rp) {
+  (void)CNt_min;
+  return (nc == 8 || nc == 21) && !rp && colterm_cg_smem_bytes(nc, T) <= 48 * 1024;
+}
 
 size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
   return (size_t)nc * 32 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
@@ -352,10 +363,9 @@ size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
 
 template <int PT, int NC>
 static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_total,
-                          const double* cwg, int ic0, int nCb, double* partM, long long* partE,
-                          unsigned long long* stats, cudaStream_t st) {
-  const int nCG = (nCb + 31) / 32;
-  const int64_t ctas = a.S * (int64_t)nCG * a.nPT * a.nChunk;
+                          const double* cwg, int ic0, int nCb, int ub0, int nUb, double* partM,
+                          long long* partE, unsigned long long* stats, cudaStream_t st) {
+  const int64_t ctas = a.S * (int64_t)nUb * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
   const size_t smb = colwarp_smem_bytes(NC, PT);
   SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
@@ -363,17 +373,17 @@ static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_tota
   SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
   baf_grid_colwarp_kernel<PT, NC><<<(unsigned)ctas, 32, smb, st>>>(
-      a, m, cwg, ic0, nCb, nCG, N_total, partM, partE, stats);
+      a, m, cwg, ic0, nCb, ub0, nUb, N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
 
-// Pre-pass + grid kernel over the shard's columns, as many 32-column groups per launch as
-// fit cw_bytes.
+// Pre-pass + grid kernel over the span's column groups that hold units of this launch, as
+// many 32-column groups per launch as fit cw_bytes.
 int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_total,
                     void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
                     cudaStream_t st, unsigned long long* stats) {
-  if (!baf_colwarp_supported(m.nc, a.rp != 0))
+  if (!baf_colwarp_supported(m.nc, m.CNt_min, m.T, a.rp != 0))
     return fail(SQZ_ERR_ARG, "column-per-lane kernel: unsupported model");
   if (PT != 16 && PT != 32)
     return fail(SQZ_ERR_ARG, "column-per-lane kernel: ploidy tile must be 16 or 32");
@@ -381,16 +391,25 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
   if (groups < 1) return fail(SQZ_ERR_SIZE, "column-per-lane kernel needs room for 32 columns");
   if (groups > 2047) groups = 2047;
   double* cwg = (double*)cw_buf;
-  const size_t pre_smem = (size_t)(m.T + 2 * m.nc) * 32 * sizeof(double);
-  for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += groups * 32) {
-    const int nCb = (int)((a.nCs - ic0 < groups * 32) ? (a.nCs - ic0) : groups * 32);
+  const size_t pre_smem = colterm_cg_smem_bytes(m.nc, m.T);
+  const int64_t u_end = (int64_t)a.u_first + a.nU;       // units of this launch: [u_first, u_end)
+  const int64_t g_lo = a.u_first / a.nPT, g_hi = (u_end + a.nPT - 1) / a.nPT;  // groups touched
+  for (int64_t g0 = g_lo; g0 < g_hi; g0 += groups) {
+    const int64_t g1 = g0 + groups < g_hi ? g0 + groups : g_hi;
+    const int64_t ic0 = g0 * 32;
+    const int nCb = (int)((a.nCs - ic0 < (g1 - g0) * 32) ? (a.nCs - ic0) : (g1 - g0) * 32);
+    // units of the batch, counted from its first group
+    const int64_t ua = (a.u_first > g0 * a.nPT ? a.u_first : g0 * a.nPT) - g0 * a.nPT;
+    const int64_t ub = (u_end < g1 * a.nPT ? u_end : g1 * a.nPT) - g0 * a.nPT;
+    if (nCb <= 0 || ub <= ua) continue;
     dim3 grid((unsigned)((N_total + kPreSeg - 1) / kPreSeg), (unsigned)((nCb + 31) / 32));
     baf_colterm_cg_kernel<<<grid, 256, pre_smem, st>>>(a, m, (int)ic0, nCb, N_total,
                                                        m.nc <= 8 ? 1 : 0, cwg);
     SQZ_CUDA(cudaGetLastError());
     int rc;
-#define SQZ_CW(PTV, NCV) \
-  rc = launch_colwarp<PTV, NCV>(a, m, N_total, cwg, (int)ic0, nCb, partM, partE, stats, st)
+#define SQZ_CW(PTV, NCV)                                                                  \
+  rc = launch_colwarp<PTV, NCV>(a, m, N_total, cwg, (int)ic0, nCb, (int)ua, (int)(ub - ua), \
+                                partM, partE, stats, st)
     if (m.nc == 8) {
       if (PT == 16) SQZ_CW(16, 8);
       else SQZ_CW(32, 8);

@@ -79,12 +79,11 @@ baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
   __shared__ unsigned redBad[8];
 
   int64_t b = blockIdx.x;
-  const int pt = (int)(b % a.nPT);
-  b /= a.nPT;
-  const int ic = (int)(b % a.nCs);
-  b /= a.nCs;
+  const int u = a.u_first + (int)(b % a.nU);  // unit (column, tile) of the span
+  b /= a.nU;
   const int chunk = (int)(b % a.nChunk);
   const int64_t smp = b / a.nChunk;
+  const int ic = u / a.nPT, pt = u - ic * a.nPT;
   const int p0 = pt * PT;
   const int tid = threadIdx.x;
 
@@ -146,12 +145,15 @@ baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
       bk_n = a.bk[sn];
     }
     double qmin[PT];
-    double sel[RP ? PT : 1];
+    double sel[RP ? PT : 1], q2[RP ? PT : 1];  // q2: runner-up ratio score (ratio.priority)
 #pragma unroll
     for (int j = 0; j < PT; ++j) qmin[j] = INF;
     if (RP) {
 #pragma unroll
-      for (int j = 0; j < (RP ? PT : 1); ++j) sel[j] = 1.0;
+      for (int j = 0; j < (RP ? PT : 1); ++j) {
+        sel[j] = 1.0;
+        q2[j] = INF;
+      }
     }
     int t = 0;
     for (int c = 0; c < m.nc; ++c) {
@@ -198,11 +200,21 @@ baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
           // ratio.priority: CNt chosen on the ratio score alone (R/bayes.R:81-88)
           double ar = tt * wc;
           if (ar < qmin[j]) {
+            q2[RP ? j : 0] = qmin[j];
             qmin[j] = ar;
             sel[RP ? j : 0] = u;
+          } else if (ar < q2[RP ? j : 0]) {
+            q2[RP ? j : 0] = ar;
           }
         }
       }
+    }
+    if (RP) {
+      // near-tie between the two best ratio scores: the reference ranks them on
+      // dt() + log(prior) (R/bayes.R:81), which may order them the other way -> repair
+#pragma unroll
+      for (int j = 0; j < (RP ? PT : 1); ++j)
+        if (q2[j] <= qmin[j] * (1.0 + 1e-12)) bad |= 1u << j;
     }
 #pragma unroll
     for (int j = 0; j < PT; ++j) P[j] *= RP ? qmin[j] * sel[RP ? j : 0] : qmin[j];
@@ -247,14 +259,20 @@ baf_grid_fast_kernel(BafGridArgs a, CnModel m, double* __restrict__ partM,
 }
 
 // ---- finalize: LPP[g] = (n + nB) k5 - 3 (E ln2 + M) in double-double ----------------
+// One thread per (sample, grid point of the span); points outside the launch's units are
+// left alone.  The result goes to every destination in a.outs (this GPU's buffer and, for
+// a multi-GPU fit, the same offset of each peer's buffer over NVLink).
 __global__ void baf_grid_finalize_kernel(BafGridArgs a, const double* __restrict__ partM,
                                          const long long* __restrict__ partE,
-                                         double* __restrict__ out, int* __restrict__ fix_list,
+                                         int* __restrict__ fix_list,
                                          int* __restrict__ fix_count) {
   const int64_t Gs = (int64_t)a.nCs * a.nP;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.S * Gs) return;
   const int64_t smp = i / Gs;
+  const int64_t g = i - smp * Gs;
+  const int ic = (int)(g / a.nP), ip = (int)(g - (int64_t)ic * a.nP);
+  if (!in_units(a, ic, ip)) return;
   double M = 0.;
   long long E = 0;
   for (int ch = 0; ch < a.nChunk; ++ch) {
@@ -279,7 +297,7 @@ __global__ void baf_grid_finalize_kernel(BafGridArgs a, const double* __restrict
   double er = ((p1 - (r - b2)) + (-p3 - b2)) + (e1 - e3);
   double res = r + er;
   if (n == 0) res = 0.;
-  out[i] = res;
+  store_result(a, smp, ic, ip, res);
   if (isnan(res)) {
     int k = atomicAdd(fix_count, 1);
     fix_list[k] = (int)i;
@@ -355,7 +373,7 @@ __device__ __forceinline__ void build_point_model(const CnModel& m, double cell,
 // null, every point (SQZ_MODE_FAITHFUL).
 __global__ void __launch_bounds__(256)
 baf_grid_faithful_kernel(BafGridArgs a, CnModel m, const int* __restrict__ fix_list,
-                         const int* __restrict__ fix_count, double* __restrict__ out) {
+                         const int* __restrict__ fix_count) {
   extern __shared__ double sm[];
   double* lratio = sm;       // [nc]
   double* baf = sm + m.nc;   // [T]
@@ -366,6 +384,7 @@ baf_grid_faithful_kernel(BafGridArgs a, CnModel m, const int* __restrict__ fix_l
     const int64_t i = fix_list ? (int64_t)fix_list[item] : item;
     const int64_t smp = i / Gs, g = i - smp * Gs;
     const int ic = (int)(g / a.nP), ip = (int)(g - (int64_t)ic * a.nP);
+    if (!fix_list && !in_units(a, ic, ip)) continue;  // block-uniform
     __syncthreads();
     build_point_model(m, a.cell[ic], a.ploidy[ip], a.adr[smp], lratio, baf);
     __syncthreads();
@@ -399,7 +418,7 @@ baf_grid_faithful_kernel(BafGridArgs a, CnModel m, const int* __restrict__ fix_l
         DD o{red[0][w], red[1][w], red[2][w]};
         dd_merge(tot, o);
       }
-      out[i] = dd_value(tot);
+      store_result(a, smp, ic, ip, dd_value(tot));
     }
   }
 }
@@ -484,11 +503,15 @@ static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 // ---- optional per-kernel timing (sqz_profile_*): CUDA events recorded on the launch
 // stream around the three phases of a fast-mode grid call, read back after the caller
 // has synchronised.  Off by default; bench.py turns it on for the roofline numbers.
+// All of this state is guarded by g_prof_mu: grid calls may come from several host
+// threads (one per device in the host entry points).
 struct ProfSet {
   cudaEvent_t ev[4];
   int path = 0;                    // 0 fused, 1 split, 2 pruned (segment lanes), 3 pruned (column lanes)
   unsigned long long n_eval = 0;   // (segment, tile, copy number) evaluations, pruned path
+  int launches = 0;                // kernels launched by this call
 };
+static std::mutex g_prof_mu;
 static bool g_prof_on = false;
 static int g_prof_dev = -1;
 static int g_prof_n = 0;
@@ -496,16 +519,21 @@ static const int kProfMax = 4096;
 static std::vector<ProfSet>* g_prof = nullptr;
 
 int profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   g_prof_on = on != 0;
   g_prof_n = 0;
   return SQZ_OK;
 }
 
 static ProfSet* prof_next() {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   if (!g_prof_on) return nullptr;
   int dev = -1;
   if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-  if (!g_prof) g_prof = new std::vector<ProfSet>();
+  if (!g_prof) {
+    g_prof = new std::vector<ProfSet>();
+    g_prof->reserve(kProfMax);  // pointers handed out below stay valid
+  }
   if (dev != g_prof_dev) {  // events belong to a device: start over on a device change
     for (auto& p : *g_prof)
       for (int k = 0; k < 4; ++k) cudaEventDestroy(p.ev[k]);
@@ -523,27 +551,34 @@ static ProfSet* prof_next() {
   ProfSet* r = &(*g_prof)[g_prof_n++];
   r->path = 0;
   r->n_eval = 0;
+  r->launches = 0;
   return r;
 }
 
-// kernel path and candidate-evaluation count of the calls recorded since profile_enable(1)
-// (read before profile_collect resets them; the caller has synchronised)
-int profile_counters(int* path, unsigned long long* n_eval) {
+// kernel path, candidate-evaluation count and kernel-launch count of the calls recorded
+// since profile_enable(1) (read before profile_collect resets them; the caller has
+// synchronised)
+int profile_counters(int* path, unsigned long long* n_eval, long long* launches) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   int p = 0;
   unsigned long long n = 0;
+  long long l = 0;
   if (g_prof)
     for (int i = 0; i < g_prof_n; ++i) {
       p = (*g_prof)[i].path;
       n += (*g_prof)[i].n_eval;
+      l += (*g_prof)[i].launches;
     }
   if (path) *path = p;
   if (n_eval) *n_eval = n;
+  if (launches) *launches = l;
   return SQZ_OK;
 }
 
 // sums (ms) of prep / fast kernel / finalize+repair over the calls recorded since
 // profile_enable(1); the caller must have synchronised the stream(s).
 int profile_collect(double* ms3, int* n_calls) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
   double acc[3] = {0, 0, 0};
   int n = 0;
   if (g_prof)
@@ -571,9 +606,14 @@ int profile_collect(double* ms3, int* n_calls) {
   return SQZ_OK;
 }
 
+// ---- planning -----------------------------------------------------------------------
+// Everything here is a function of the WHOLE grid (nC x nP), the segment table (N_total,
+// S) and the model -- never of the shard a launch works on -- so that a grid point gets
+// the same bits from any shard and any GPU count (see sqz_baf_grid.cuh).
 struct GridPlan {
+  int family;  // 0 fused, 1 split, 2 pruned (segment per lane), 3 pruned (column per lane)
   int PT, nPT, nChunk, threads;
-  int colwarp;  // 1: column-per-lane pruned kernel (sqz_baf_colwarp.cu)
+  int W;       // columns per unit: 32 for family 3, else 1
 };
 
 static int env_int(const char* name, int dflt) {
@@ -597,16 +637,22 @@ static int prune_mode(int nc, bool monotone, bool rp) {
   return e < 0 ? (nc <= 12 ? 1 : 0) : (e != 0);
 }
 
-// Chunk count of the column-per-lane kernel.  It follows the segment table only (not the
-// grid, the shard or the scratch size), so a shard of a grid and the whole grid, or two
-// scratch sizes, give the same bits.  Every warp of that kernel walks all segments of its
-// chunk: at least 64 per chunk, at most 64 chunks, fewer for a cohort (the samples already
-// fill the machine, and every chunk costs a slab of partial results).
+// Chunk count of the column-per-lane kernel.  It follows the segment table only.  Every
+// warp of that kernel walks all segments of its chunk: at least 64 per chunk, at most
+// kColwarpMaxChunks chunks, fewer for a cohort (the samples already fill the machine, and
+// every chunk costs a slab of partial results).
+constexpr int64_t kColwarpMaxChunks = 128;
 static int64_t colwarp_chunks(int64_t N_total, int64_t S) {
   const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
-  int64_t k = avg / 64, top = S > 0 ? 2048 / S : 64;
+  int64_t top = S > 0 ? 2048 / S : 64;
   if (top > 64) top = 64;
+  int64_t k = avg / 64;
   if (k > top) k = top;
+  // long tables of a single sample: up to 128 chunks of 512 segments or more, so that an
+  // eighth of the fine grid (one GPU of eight) still gives every SM several waves of
+  // one-warp CTAs and a short idle tail
+  const int64_t cap = env_int("SQZ_CW_MAXCHUNKS", (int)kColwarpMaxChunks);
+  if (S == 1 && avg / 512 > 64) k = avg / 512 < cap ? avg / 512 : cap;
   return k < 1 ? 1 : k;
 }
 
@@ -621,57 +667,59 @@ static int64_t max_chunks(int64_t N_total, int64_t S) {
   return a < 1 ? 1 : a;
 }
 
-// Ploidy tile of the column-per-lane kernel, or 0 when the segment-per-lane pruned kernel is
-// the better choice.  The column-per-lane kernel runs one warp per (32 columns, tile, chunk)
-// and there are 8 warp slots per SM: it wins when those units fill the machine for several
-// waves (measured: tools/colwarp_vs_pruned.py), and when few lanes of the last 32-column
-// group idle.  32-wide tiles when there are enough units, else 16-wide (twice the units).
-static int colwarp_tile(int nc, bool rp, int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
+// Ploidy tile of the column-per-lane kernel, or 0 when a segment-per-lane kernel is the
+// better choice for this grid.  The column-per-lane kernel runs one warp per (32 columns,
+// tile, chunk) and there are 8 warp slots per SM: it wins when those units fill the
+// machine for several waves (measured: tools/colwarp_vs_pruned.py), and when few lanes of
+// the last 32-column group idle.  32-wide tiles when there are enough units, else 16-wide.
+static int colwarp_tile(const CnModel& m, bool rp, int64_t N_total, int64_t S, int64_t nP,
+                        int64_t nC) {
   const int e = env_int("SQZ_COLWARP", -1);  // 0/1 override (experiments and tests only)
-  if (e == 0 || !baf_colwarp_supported(nc, rp) || N_total <= 0) return 0;
+  if (e == 0 || !baf_colwarp_supported(m.nc, m.CNt_min, m.T, rp) || N_total <= 0) return 0;
   const int pt_env = env_int("SQZ_PT", 0);
   if (e == 1) return (pt_env == 16 || pt_env == 32) ? pt_env : (nP <= 96 ? 16 : 32);
-  const int64_t groups = (nCs + 31) / 32;
-  if (nCs * 10 < groups * 32 * 6) return 0;
+  const int64_t groups = (nC + 31) / 32;
+  if (nC * 10 < groups * 32 * 6) return 0;
   const int64_t slots = 148 * 8, ch = colwarp_chunks(N_total, S);
   const int64_t u32 = S * groups * ((nP + 31) / 32) * ch, u16 = S * groups * ((nP + 15) / 16) * ch;
-  if (nc > 8)  // CNt 0..20: a coarse ploidy axis keeps 4-6 copy numbers alive per warp and
-               // the plain split kernel is as fast (91 x 61 grid: 1.44 vs 1.50 ms)
+  if (m.nc > 8)  // CNt 0..20: a coarse ploidy axis keeps 4-6 copy numbers alive per warp and
+                 // the plain split kernel is as fast (91 x 61 grid: 1.44 vs 1.50 ms)
     return (nP >= 200 && u16 >= 2 * slots) ? 16 : 0;
   // 32-wide tiles need fewer instructions per evaluation; 16-wide ones give twice the units
   // and a cheaper per-chunk prologue.  Measured (tools/colwarp_vs_pruned.py,
   // tools/shard_tile_width.py): 32 wins from 6 waves of units on, and from 2 waves on when
-  // the chunks are long (config 3 shards: 5.45 vs 7.01 ms at 113 columns).
+  // the chunks are long.
   const int64_t per_chunk = (S > 0 ? (N_total + S - 1) / S : 0) / ch;
-  if (nP > 96 && (u32 >= 6 * slots || (u32 >= 2 * slots && per_chunk >= 1000))) return 32;
+  if (nP > 96 && (u32 >= 6 * slots || (u32 >= 2 * slots && per_chunk >= 500))) return 32;
   if (u16 >= 3 * slots) return 16;
   return 0;
 }
 
-// Plan for the column-per-lane kernel.
-static GridPlan plan_colwarp(int64_t N_total, int64_t S, int64_t nP, int PT) {
+static GridPlan plan_fit(int64_t N_total, int64_t S, int64_t nP, int64_t nC, const CnModel& m,
+                         bool rp, bool monotone, bool allow_colwarp = true) {
   GridPlan g;
-  g.colwarp = 1;
-  g.PT = PT;
-  g.nPT = (int)((nP + g.PT - 1) / g.PT);
-  g.threads = 32;  // one warp per CTA
-  g.nChunk = (int)colwarp_chunks(N_total, S);
-  const int ch_env = env_int("SQZ_CHUNKS", 0);
-  if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
-  return g;
-}
-
-static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
-                          const CnModel* m, bool rp = false, bool pruned = false) {
-  GridPlan g;
-  g.colwarp = 0;
+  const int cw_pt = (allow_colwarp && monotone && env_int("SQZ_PRUNE", 1) != 0)
+                        ? colwarp_tile(m, rp, N_total, S, nP, nC) : 0;
+  if (cw_pt) {
+    g.family = 3;
+    g.W = 32;
+    g.PT = cw_pt;
+    g.nPT = (int)((nP + g.PT - 1) / g.PT);
+    g.threads = 32;  // one warp per CTA
+    g.nChunk = (int)colwarp_chunks(N_total, S);
+    const int ch_env = env_int("SQZ_CHUNKS", 0);
+    if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
+    return g;
+  }
+  const bool pruned = prune_mode(m.nc, monotone, rp) != 0;
+  g.family = pruned ? 2 : 1;
+  g.W = 1;
   const int cand[3] = {8, 16, 32};
   double bestc = 0;
   g.PT = 32;
-  const int nc = m ? m->nc : 8, T = m ? m->T : 20;
   for (int k = 0; k < (rp ? 2 : 3); ++k) {  // PT = 32 spills registers with ratio.priority
     int pt = cand[k];
-    double cost = (double)((nP + pt - 1) / pt) * (pt * (4.0 * nc + 1) + 2.0 * T + 2.0 * nc);
+    double cost = (double)((nP + pt - 1) / pt) * (pt * (4.0 * m.nc + 1) + 2.0 * m.T + 2.0 * m.nc);
     if (k == 0 || cost < bestc) {
       bestc = cost;
       g.PT = pt;
@@ -693,9 +741,9 @@ static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
   int per_sm = 65536 / (regs * g.threads);
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
-  // Split each sample's segments into chunks until the grid fills the machine for a
+  // Split each sample's segments into chunks until the whole grid fills the machine for a
   // few waves, then pick the chunk count with the smallest idle tail in that range.
-  const int64_t base = S * nCs * g.nPT;
+  const int64_t base = S * nC * g.nPT;
   int64_t cap = avg / ((int64_t)g.threads * 8);  // keep >= 8 segments per thread
   if (cap < 1) cap = 1;
   if (cap > 64) cap = 64;
@@ -719,6 +767,25 @@ static GridPlan plan_grid(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
   return g;
 }
 
+static bool ploidy_monotone(const double* h_ploidy, int64_t nP) {
+  if (!h_ploidy) return true;
+  bool up = true, dn = true;
+  for (int64_t i = 1; i < nP; ++i) {
+    if (!(h_ploidy[i] >= h_ploidy[i - 1])) up = false;
+    if (!(h_ploidy[i] <= h_ploidy[i - 1])) dn = false;
+  }
+  return up || dn;
+}
+
+// the most samples one batch of launches may hold: (sample, grid point) items are indexed
+// with 32-bit integers in the repair list
+static int64_t samples_per_batch(int64_t S, int64_t nP, int64_t nCs) {
+  const int64_t per = nCs * nP > 0 ? nCs * nP : 1;
+  int64_t sb = 0x7fffffffLL / per;
+  if (sb > 65535) sb = 65535;  // gridDim.y of the preparation kernel
+  return sb < S ? sb : S;
+}
+
 struct Workspace {
   double2 *rk, *bk;
   int* nB;
@@ -726,10 +793,11 @@ struct Workspace {
   double* partM;
   long long* partE;
   int *fix_list, *fix_count;
-  unsigned long long* stats;  // candidate evaluations of the pruned kernel (profiling only)
+  unsigned long long* stats;  // candidate evaluations of the pruned kernels (profiling only)
   size_t bytes;
 };
 
+// nCs = columns of the span a launch works on
 static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
   // partials are sized for the largest chunk count the planner can pick
   Workspace w;
@@ -741,7 +809,8 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
     return r;
   };
   const size_t n = (size_t)(N_total > 0 ? N_total : 1);
-  const size_t items = (size_t)(S * nCs * nP > 0 ? S * nCs * nP : 1);
+  const int64_t Sb = samples_per_batch(S, nP, nCs);
+  const size_t items = (size_t)(Sb * nCs * nP > 0 ? Sb * nCs * nP : 1);
   const int64_t want = max_chunks(N_total, S);
   w.rk = (double2*)take(n * sizeof(double2));
   w.bk = (double2*)take(n * sizeof(double2));
@@ -757,42 +826,55 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   return w;
 }
 
-// launch geometry of a fast-mode call, for reporting (bench.py roofline)
-int baf_grid_plan(int64_t N_total, int64_t S, int64_t nP, int64_t nCs, int CNt_min, int CNt_max,
-                  int CNn, int ratio_priority, int* out5) {
+// plan of a fast-mode call, for reporting (bench.py roofline) and for sharding by units:
+// out8 = {PT, nPT, chunks, threads, T, kernel family, W, units of the whole grid}
+int baf_grid_plan(int64_t N_total, int64_t S, const double* h_ploidy, int64_t nP, int64_t nC,
+                  int CNt_min, int CNt_max, int CNn, int ratio_priority, int64_t* out8) {
   CnModel m;
   bool ok;
   int rc = build_cn_model(0, CNt_min, CNt_max, CNn, nullptr, nullptr, 0, &m, &ok);
   if (rc) return rc;
-  const bool prune = prune_mode(m.nc, true, ratio_priority != 0) != 0;
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune);
-  const int cw_pt = env_int("SQZ_PRUNE", 1) != 0
-                        ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
-  if (cw_pt) g = plan_colwarp(N_total, S, nP, cw_pt);  // as baf_grid_launch decides given
-                                                       // the preferred workspace
-  out5[0] = g.PT;
-  out5[1] = g.nPT;
-  out5[2] = g.nChunk;
-  out5[3] = g.threads;
-  out5[4] = m.T;
+  const GridPlan g = plan_fit(N_total, S, nP, nC, m, ratio_priority != 0,
+                              ploidy_monotone(h_ploidy, nP));
+  out8[0] = g.PT;
+  out8[1] = g.nPT;
+  out8[2] = g.nChunk;
+  out8[3] = g.threads;
+  out8[4] = m.T;
+  out8[5] = g.family;
+  out8[6] = g.W;
+  out8[7] = ((nC + g.W - 1) / g.W) * g.nPT;
   return SQZ_OK;
+}
+
+// columns [span0, span1) that the units [u0, u1) of the whole grid touch
+static void unit_span(const GridPlan& g, int64_t nC, int64_t u0, int64_t u1, int64_t* span0,
+                      int64_t* span1) {
+  const int64_t g0 = u0 / g.nPT, g1 = (u1 + g.nPT - 1) / g.nPT;
+  *span0 = g0 * g.W;
+  *span1 = g1 * g.W < nC ? g1 * g.W : nC;
 }
 
 size_t baf_grid_workspace_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs) {
   return carve(nullptr, N_total, S, nP, nCs).bytes;
 }
 
-// minimum + room for the pre-pass output of as many columns as fit under `cap_bytes`
-size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nCs,
-                                          int n_copy_numbers, size_t cap_bytes) {
+// minimum + room for the pre-pass output of as many of the span's columns as fit under
+// `cap_bytes`; the kernel family follows the whole grid (nC columns)
+size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP, int64_t nC,
+                                          int64_t nCs, int n_copy_numbers, size_t cap_bytes) {
   const size_t base = carve(nullptr, N_total, S, nP, nCs).bytes;
   if (n_copy_numbers < 1 || n_copy_numbers > kMaxCN || nCs < 1) return base;
+  if (nC < nCs) nC = nCs;
   const size_t per_col = baf_split_column_bytes(n_copy_numbers, N_total);
   size_t cols = (size_t)nCs;
-  if (colwarp_tile(n_copy_numbers, false, N_total, S, nP, nCs)) {
+  CnModel m;
+  bool ok;
+  if (build_cn_model(0, 0, n_copy_numbers - 1, 2, nullptr, nullptr, 0, &m, &ok) == SQZ_OK &&
+      colwarp_tile(m, false, N_total, S, nP, nC)) {
     // the column-per-lane kernel would take this fit: 8 bytes per (column, copy number,
     // segment) in whole 32-column groups.  (A call that cannot use it after all --
-    // ratio.priority, unsorted ploidies -- runs the split kernel in two batches.)
+    // ratio.priority, unsorted ploidies -- runs the split kernel in batches.)
     size_t want = ((cols + 31) / 32) * baf_colwarp_group_bytes(n_copy_numbers, N_total);
     if (want < per_col) want = per_col;
     if (cap_bytes > 0 && want > cap_bytes) want = cap_bytes;
@@ -803,52 +885,106 @@ size_t baf_grid_workspace_preferred_bytes(int64_t N_total, int64_t S, int64_t nP
   return base + align256(cols * per_col);
 }
 
-int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
-                    const double* d_ratio, const double* d_sdBf, const double* d_sdr,
-                    const double* d_wBf, const double* d_wr, const double* h_ploidy,
-                    int64_t nP, const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1,
-                    const double* d_adr, int CNt_min, int CNt_max, int CNn,
-                    const double* prior_CN, const double* prior_value, int n_prior,
-                    int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
-                    cudaStream_t st, double* d_out) {
-  if (S < 0 || N_total < 0 || nP < 0 || nC < 0 || ic0 < 0 || ic1 > nC || ic0 > ic1)
-    return fail(SQZ_ERR_ARG, "negative size or bad cellularity shard");
+// the same for a shard given as units [u0, u1) of the whole grid
+size_t baf_grid_units_workspace_bytes(int64_t N_total, int64_t S, const double* h_ploidy,
+                                      int64_t nP, int64_t nC, int CNt_min, int CNt_max, int CNn,
+                                      int ratio_priority, int64_t u0, int64_t u1,
+                                      size_t cap_bytes) {
+  CnModel m;
+  bool ok;
+  if (build_cn_model(0, CNt_min, CNt_max, CNn, nullptr, nullptr, 0, &m, &ok) != SQZ_OK) return 0;
+  const GridPlan g = plan_fit(N_total, S, nP, nC, m, ratio_priority != 0,
+                              ploidy_monotone(h_ploidy, nP));
+  if (u0 < 0 || u1 < u0 || u1 > ((nC + g.W - 1) / g.W) * g.nPT) return 0;
+  if (u0 == u1) return carve(nullptr, N_total, S, nP, 1).bytes;
+  int64_t span0, span1;
+  unit_span(g, nC, u0, u1, &span0, &span1);
+  return baf_grid_workspace_preferred_bytes(N_total, S, nP, nC, span1 - span0, m.nc, cap_bytes);
+}
+
+// ---- launch ---------------------------------------------------------------------------
+// What part of the grid a call computes and where the results go.
+struct GridShard {
+  bool by_units;     // false: columns [a0, a1) -> out[S][(a1 - a0) * nP], shard-relative
+                     // true : units   [a0, a1) -> out[S][nC * nP], whole-grid layout
+  int64_t a0, a1;
+  int n_out;
+  double* outs[kMaxOut];
+};
+
+static int baf_grid_core(int64_t S, const int64_t* d_seg_off, int64_t N_total,
+                         const double* d_Bf, const double* d_ratio, const double* d_sdBf,
+                         const double* d_sdr, const double* d_wBf, const double* d_wr,
+                         const double* h_ploidy, int64_t nP, const double* h_cell, int64_t nC,
+                         const GridShard& sh, const double* d_adr, int CNt_min, int CNt_max,
+                         int CNn, const double* prior_CN, const double* prior_value,
+                         int n_prior, int ratio_priority, int mode, void* workspace,
+                         size_t workspace_bytes, cudaStream_t st, bool allow_profile) {
+  if (S < 0 || N_total < 0 || nP < 0 || nC < 0)
+    return fail(SQZ_ERR_ARG, "negative size");
   if (mode != SQZ_MODE_FAST && mode != SQZ_MODE_FAITHFUL)
     return fail(SQZ_ERR_ARG, "mode must be SQZ_MODE_FAST or SQZ_MODE_FAITHFUL");
-  const int64_t nCs = ic1 - ic0;
-  if (S == 0 || nCs == 0 || nP == 0) return SQZ_OK;
-  if (S * nCs * nP > 0x7fffffffLL)
-    return fail(SQZ_ERR_SIZE, "more than 2^31-1 (sample, grid point) items in one shard");
+  if (sh.n_out < 1 || sh.n_out > kMaxOut)
+    return fail(SQZ_ERR_ARG, "between 1 and 8 output buffers");
   CnModel m;
   bool fast_ok;
   int rc = build_cn_model(0, CNt_min, CNt_max, CNn, prior_CN, prior_value, n_prior, &m,
                           &fast_ok);
   if (rc) return rc;
+  const bool rp = ratio_priority != 0;
+  // candidate pruning relies on the residual being monotone over a ploidy tile
+  const bool mono = ploidy_monotone(h_ploidy, nP);
+  GridPlan g = plan_fit(N_total, S, nP, nC, m, rp, mono);
+
+  // the span of columns this call works on, and its units
+  int64_t span0, span1, u_first, nU;
+  if (!sh.by_units) {
+    if (sh.a0 < 0 || sh.a1 > nC || sh.a0 > sh.a1)
+      return fail(SQZ_ERR_ARG, "bad cellularity shard");
+    span0 = sh.a0;
+    span1 = sh.a1;
+    u_first = 0;
+    nU = ((span1 - span0 + g.W - 1) / g.W) * g.nPT;
+  } else {
+    const int64_t n_units = ((nC + g.W - 1) / g.W) * g.nPT;
+    if (sh.a0 < 0 || sh.a1 > n_units || sh.a0 > sh.a1)
+      return fail(SQZ_ERR_ARG, "bad unit shard (see sqz_baf_grid_plan for the unit count)");
+    unit_span(g, nC, sh.a0, sh.a1, &span0, &span1);
+    u_first = sh.a0 - (sh.a0 / g.nPT) * g.nPT;
+    nU = sh.a1 - sh.a0;
+  }
+  const int64_t nCs = span1 - span0;
+  if (S == 0 || nCs <= 0 || nP == 0 || nU == 0) return SQZ_OK;
+  if (nCs * nP > 0x7fffffffLL)
+    return fail(SQZ_ERR_SIZE, "more than 2^31-1 grid points in one shard");
+  if (S > 65535 * 64LL) return fail(SQZ_ERR_SIZE, "more than 4,194,240 samples in one call");
+  for (int k = 0; k < sh.n_out; ++k)
+    if (!sh.outs[k]) return fail(SQZ_ERR_ARG, "an output buffer is null");
   if (!workspace || ((uintptr_t)workspace & 255))
     return fail(SQZ_ERR_ARG, "workspace must be non-null and 256-byte aligned");
   Workspace w = carve(workspace, N_total, S, nP, nCs);
   if (w.bytes > workspace_bytes) return fail(SQZ_ERR_SIZE, "workspace too small");
 
   SQZ_CUDA(cudaMemcpyAsync(w.ploidy, h_ploidy, nP * sizeof(double), cudaMemcpyHostToDevice, st));
-  SQZ_CUDA(cudaMemcpyAsync(w.cell, h_cell + ic0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
+  SQZ_CUDA(cudaMemcpyAsync(w.cell, h_cell + span0, nCs * sizeof(double), cudaMemcpyHostToDevice, st));
 
-  // candidate pruning relies on the residual being monotone over a ploidy tile
-  bool mono_up = true, mono_dn = true;
-  for (int64_t i = 1; i < nP; ++i) {
-    if (!(h_ploidy[i] >= h_ploidy[i - 1])) mono_up = false;
-    if (!(h_ploidy[i] <= h_ploidy[i - 1])) mono_dn = false;
-  }
-  const int prune = prune_mode(m.nc, mono_up || mono_dn, ratio_priority != 0);
-  GridPlan g = plan_grid(N_total, S, nP, nCs, &m, ratio_priority != 0, prune != 0);
   // pre-pass scratch behind the fixed part of the workspace
   char* cw_buf = (char*)workspace + w.bytes;
   const size_t cw_bytes = workspace_bytes > w.bytes ? workspace_bytes - w.bytes : 0;
-  const int cw_pt = (mono_up || mono_dn) && env_int("SQZ_PRUNE", 1) != 0
-                        ? colwarp_tile(m.nc, ratio_priority != 0, N_total, S, nP, nCs) : 0;
-  if (cw_pt && cw_bytes >= baf_colwarp_group_bytes(m.nc, N_total))
-    g = plan_colwarp(N_total, S, nP, cw_pt);  // column-per-lane kernel: room for >= 32 columns
+  if (g.family == 3 && cw_bytes < baf_colwarp_group_bytes(m.nc, N_total)) {
+    // no room for one 32-column group of pre-pass output: segment-per-lane kernels
+    g = plan_fit(N_total, S, nP, nC, m, rp, mono, false);
+    if (sh.by_units) return fail(SQZ_ERR_SIZE, "workspace too small for a unit shard of the "
+                                               "column-per-lane kernel");
+    nU = nCs * g.nPT;
+  }
+  const bool use_split = g.family == 3 ||
+                         (env_int("SQZ_SPLIT", 1) != 0 && N_total > 0 &&
+                          baf_split_supported(m.nc, g.PT, g.threads) &&
+                          cw_bytes >= baf_split_column_bytes(m.nc, N_total));
+  if (!use_split) g.family = 0;
+
   BafGridArgs a;
-  a.S = S;
   a.seg_off = d_seg_off;
   a.Bf = d_Bf;
   a.ratio = d_ratio;
@@ -858,62 +994,80 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
   a.wr = d_wr;
   a.rk = w.rk;
   a.bk = w.bk;
-  a.nB = w.nB;
-  a.adr = d_adr;
   a.ploidy = w.ploidy;
   a.cell = w.cell;
   a.nP = (int)nP;
   a.nCs = (int)nCs;
   a.nPT = g.nPT;
   a.nChunk = g.nChunk;
-  a.rp = ratio_priority ? 1 : 0;
+  a.PT = g.PT;
+  a.W = g.W;
+  a.u_first = (int)u_first;
+  a.nU = (int)nU;
+  a.rp = rp ? 1 : 0;
   a.t5 = dt5_const();
+  a.out_sS = sh.by_units ? nC * nP : nCs * nP;
+  a.out_col0 = sh.by_units ? span0 : 0;
+  a.n_out = sh.n_out;
 
   const size_t sm_faith = (size_t)(m.nc + m.T) * sizeof(double);
   const int faithful_ctas = 148 * 4;
-  if (mode == SQZ_MODE_FAITHFUL || !fast_ok) {
-    baf_grid_faithful_kernel<<<faithful_ctas, 256, sm_faith, st>>>(a, m, nullptr, nullptr, d_out);
-    SQZ_CUDA(cudaGetLastError());
-    return SQZ_OK;
-  }
+  const bool fast = mode == SQZ_MODE_FAST && fast_ok;
+  ProfSet* prof = (fast && allow_profile) ? prof_next() : nullptr;
+  int launches = 0;
 
-  SQZ_CUDA(cudaMemsetAsync(w.nB, 0, S * sizeof(int), st));
-  SQZ_CUDA(cudaMemsetAsync(w.fix_count, 0, sizeof(int), st));
-  ProfSet* prof = prof_next();
-  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[0], st));
-  {
+  if (fast) {
+    SQZ_CUDA(cudaMemsetAsync(w.nB, 0, S * sizeof(int), st));
+    if (prof) {
+      SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
+      SQZ_CUDA(cudaEventRecord(prof->ev[0], st));
+    }
+    // per-segment preparation, all samples (gridDim.y holds at most 65535 of them)
     const int64_t avg = (N_total + S - 1) / S;
     int bx = (int)((avg + 255) / 256);
     if (bx < 1) bx = 1;
     if (bx > 1024) bx = 1024;
-    dim3 grid(bx, (unsigned)S);
-    if (S > 65535) return fail(SQZ_ERR_SIZE, "more than 65535 samples in one call");
-    baf_prep_kernel<<<grid, 256, 0, st>>>(a, w.rk, w.bk, w.nB);
-    SQZ_CUDA(cudaGetLastError());
-  }
-  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[1], st));
-  // Split path when the workspace has room for at least one column of pre-pass output
-  // (sqz_baf_grid_workspace_preferred_bytes); fused kernel otherwise.
-  const bool use_split = env_int("SQZ_SPLIT", 1) != 0 && N_total > 0 &&
-                         (g.colwarp || baf_split_supported(m.nc, g.PT, g.threads)) &&
-                         cw_bytes >= baf_split_column_bytes(m.nc, N_total);
-  if (use_split) {
-    if (prof) SQZ_CUDA(cudaMemsetAsync(w.stats, 0, sizeof(unsigned long long), st));
-    rc = g.colwarp ? baf_colwarp_run(a, m, g.PT, N_total, cw_buf, cw_bytes, w.partM, w.partE,
-                                      st, prof ? w.stats : nullptr)
-                    : baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
-                                    w.partE, st, prune != 0, prof ? w.stats : nullptr);
-    if (prof) {
-      prof->path = g.colwarp ? 3 : (prune ? 2 : 1);
-      SQZ_CUDA(cudaMemcpyAsync(&prof->n_eval, w.stats, sizeof(unsigned long long),
-                               cudaMemcpyDeviceToHost, st));
+    for (int64_t sa = 0; sa < S; sa += 65535) {
+      const int64_t sb = sa + 65535 < S ? sa + 65535 : S;
+      BafGridArgs ap = a;
+      ap.S = sb - sa;
+      ap.seg_off = d_seg_off + sa;
+      dim3 grid(bx, (unsigned)(sb - sa));
+      baf_prep_kernel<<<grid, 256, 0, st>>>(ap, w.rk, w.bk, w.nB + sa);
+      SQZ_CUDA(cudaGetLastError());
+      ++launches;
     }
-    if (rc) return rc;
-  } else {
-    const int64_t ctas = S * nCs * (int64_t)g.nPT * g.nChunk;
-    if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-    const size_t smb = (size_t)(m.nc * g.PT + m.T) * sizeof(double);
-    const bool rp = a.rp != 0;
+    if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[1], st));
+  }
+
+  // batches of samples: (sample, grid point) items are indexed with 32-bit integers
+  const int64_t Sb = samples_per_batch(S, nP, nCs);
+  for (int64_t sa = 0; sa < S; sa += Sb) {
+    const int64_t sb = sa + Sb < S ? sa + Sb : S;
+    a.S = sb - sa;
+    a.seg_off = d_seg_off + sa;
+    a.adr = d_adr + sa;
+    a.nB = w.nB + sa;
+    for (int k = 0; k < sh.n_out; ++k) a.outs[k] = sh.outs[k] + sa * a.out_sS;
+    if (!fast) {
+      baf_grid_faithful_kernel<<<faithful_ctas, 256, sm_faith, st>>>(a, m, nullptr, nullptr);
+      SQZ_CUDA(cudaGetLastError());
+      continue;
+    }
+    SQZ_CUDA(cudaMemsetAsync(w.fix_count, 0, sizeof(int), st));
+    if (use_split) {
+      rc = g.family == 3
+               ? baf_colwarp_run(a, m, g.PT, N_total, cw_buf, cw_bytes, w.partM, w.partE, st,
+                                 prof ? w.stats : nullptr)
+               : baf_split_run(a, m, g.PT, g.threads, N_total, cw_buf, cw_bytes, w.partM,
+                               w.partE, st, g.family == 2, prof ? w.stats : nullptr);
+      if (rc) return rc;
+      launches += 2;  // pre-pass + grid kernel (per batch of columns; one batch when the
+                      // preferred workspace is given)
+    } else {
+      const int64_t ctas = a.S * nU * g.nChunk;
+      if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
+      const size_t smb = (size_t)(m.nc * g.PT + m.T) * sizeof(double);
 #define SQZ_LAUNCH_FAST(PTV)                                                              \
   do {                                                                                    \
     if (rp)                                                                               \
@@ -921,24 +1075,79 @@ int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const 
     else                                                                                  \
       baf_grid_fast_kernel<PTV, false><<<(unsigned)ctas, g.threads, smb, st>>>(a, m, w.partM, w.partE); \
   } while (0)
-    if (g.PT == 8) SQZ_LAUNCH_FAST(8);
-    else if (g.PT == 16) SQZ_LAUNCH_FAST(16);
-    else SQZ_LAUNCH_FAST(32);
+      if (g.PT == 8) SQZ_LAUNCH_FAST(8);
+      else if (g.PT == 16) SQZ_LAUNCH_FAST(16);
+      else SQZ_LAUNCH_FAST(32);
 #undef SQZ_LAUNCH_FAST
-    SQZ_CUDA(cudaGetLastError());
-  }
-  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[2], st));
-  {
-    const int64_t items = S * nCs * nP;
+      SQZ_CUDA(cudaGetLastError());
+      ++launches;
+    }
+    if (prof && sb == S) SQZ_CUDA(cudaEventRecord(prof->ev[2], st));
+    const int64_t items = a.S * nCs * nP;
     baf_grid_finalize_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(
-        a, w.partM, w.partE, d_out, w.fix_list, w.fix_count);
+        a, w.partM, w.partE, w.fix_list, w.fix_count);
     SQZ_CUDA(cudaGetLastError());
     baf_grid_faithful_kernel<<<faithful_ctas, 256, sm_faith, st>>>(a, m, w.fix_list,
-                                                                  w.fix_count, d_out);
+                                                                  w.fix_count);
     SQZ_CUDA(cudaGetLastError());
+    launches += 2;
   }
-  if (prof) SQZ_CUDA(cudaEventRecord(prof->ev[3], st));
+  if (prof) {
+    prof->path = g.family;
+    prof->launches = launches;
+    SQZ_CUDA(cudaMemcpyAsync(&prof->n_eval, w.stats, sizeof(unsigned long long),
+                             cudaMemcpyDeviceToHost, st));
+    SQZ_CUDA(cudaEventRecord(prof->ev[3], st));
+  }
   return SQZ_OK;
+}
+
+// column shard [ic0, ic1): results in d_out[S][(ic1 - ic0) * nP]
+int baf_grid_launch(int64_t S, const int64_t* d_seg_off, int64_t N_total, const double* d_Bf,
+                    const double* d_ratio, const double* d_sdBf, const double* d_sdr,
+                    const double* d_wBf, const double* d_wr, const double* h_ploidy,
+                    int64_t nP, const double* h_cell, int64_t nC, int64_t ic0, int64_t ic1,
+                    const double* d_adr, int CNt_min, int CNt_max, int CNn,
+                    const double* prior_CN, const double* prior_value, int n_prior,
+                    int ratio_priority, int mode, void* workspace, size_t workspace_bytes,
+                    cudaStream_t st, double* d_out, bool allow_profile) {
+  GridShard sh;
+  sh.by_units = false;
+  sh.a0 = ic0;
+  sh.a1 = ic1;
+  sh.n_out = 1;
+  sh.outs[0] = d_out;
+  if (S > 0 && nP > 0 && ic1 > ic0 && !d_out) return fail(SQZ_ERR_ARG, "output buffer is null");
+  if (!d_out) sh.outs[0] = (double*)workspace;  // nothing will be written
+  return baf_grid_core(S, d_seg_off, N_total, d_Bf, d_ratio, d_sdBf, d_sdr, d_wBf, d_wr,
+                       h_ploidy, nP, h_cell, nC, sh, d_adr, CNt_min, CNt_max, CNn, prior_CN,
+                       prior_value, n_prior, ratio_priority, mode, workspace, workspace_bytes,
+                       st, allow_profile);
+}
+
+// unit shard [u0, u1) of the whole grid: results at their final place of every buffer in
+// d_outs (each S x nC x nP, ploidy fastest) -- this GPU's and, over NVLink, its peers'
+int baf_grid_launch_units(int64_t S, const int64_t* d_seg_off, int64_t N_total,
+                          const double* d_Bf, const double* d_ratio, const double* d_sdBf,
+                          const double* d_sdr, const double* d_wBf, const double* d_wr,
+                          const double* h_ploidy, int64_t nP, const double* h_cell, int64_t nC,
+                          int64_t u0, int64_t u1, const double* d_adr, int CNt_min,
+                          int CNt_max, int CNn, const double* prior_CN,
+                          const double* prior_value, int n_prior, int ratio_priority, int mode,
+                          void* workspace, size_t workspace_bytes, cudaStream_t st,
+                          double* const* d_outs, int n_out) {
+  if (n_out < 1 || n_out > kMaxOut || !d_outs)
+    return fail(SQZ_ERR_ARG, "between 1 and 8 output buffers");
+  GridShard sh;
+  sh.by_units = true;
+  sh.a0 = u0;
+  sh.a1 = u1;
+  sh.n_out = n_out;
+  for (int k = 0; k < n_out; ++k) sh.outs[k] = d_outs[k];
+  return baf_grid_core(S, d_seg_off, N_total, d_Bf, d_ratio, d_sdBf, d_sdr, d_wBf, d_wr,
+                       h_ploidy, nP, h_cell, nC, sh, d_adr, CNt_min, CNt_max, CNn, prior_CN,
+                       prior_value, n_prior, ratio_priority, mode, workspace, workspace_bytes,
+                       st, true);
 }
 
 int baf_point_launch(const double* d_Bf, const double* d_ratio, const double* d_sdBf,
@@ -1002,6 +1211,13 @@ extern "C" int sqz_baf_grid_dev_noalloc(
     const double* prior_value, int n_prior, int ratio_priority, int mode, void* stream,
     double* d_lpp_sum_out) {
   using namespace sqz;
+  {
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev < 1) {
+      cudaGetLastError();
+      return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+    }
+  }
   if (S < 0 || N_total < 0 || nP < 0 || nC < 0 || ic0 < 0 || ic1 > nC || ic0 > ic1)
     return fail(SQZ_ERR_ARG, "negative size or bad cellularity shard");
   const size_t need = baf_grid_workspace_bytes(N_total, S, nP, ic1 - ic0);
@@ -1017,15 +1233,12 @@ extern "C" int sqz_baf_grid_dev_noalloc(
   void* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);
   if (rc) return rc;
-  // the optional per-kernel timing creates CUDA events on first use; keep it out of a
-  // path that promises not to allocate
-  const bool prof_was_on = g_prof_on;
-  g_prof_on = false;
+  // the optional per-kernel timing creates CUDA events on first use: it is switched off for
+  // this call (allow_profile = false), a path that promises not to allocate
   rc = baf_grid_launch(S, d_seg_offsets, N_total, d_Bf, d_depth_ratio, d_sd_Bf, d_sd_ratio,
                        d_weight_Bf, d_weight_ratio, ploidy, nP, cellularity, nC, ic0, ic1,
                        d_avg_depth_ratio, CNt_min, CNt_max, CNn, prior_CN, prior_value,
                        n_prior, ratio_priority, mode, scratch, kNoAllocScratchBytes,
-                       (cudaStream_t)stream, d_lpp_sum_out);
-  g_prof_on = prof_was_on;
+                       (cudaStream_t)stream, d_lpp_sum_out, false);
   return rc;
 }

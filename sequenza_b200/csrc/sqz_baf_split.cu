@@ -6,13 +6,14 @@
 // has nP/PT ploidy tiles, so the fused kernel recomputes it nP/PT times.  Here:
 //
 //   baf_colterm_kernel   one thread per (cellularity, segment): the min over B for every
-//                        copy number, stored as (wub, sqrt(wub)) in a column-major scratch
+//                        copy number, stored as sqrt(wub) (8 bytes; wub is its square, one
+//                        DMUL per copy number where it is needed) in a column-major scratch
 //                        [column][CNt][segment] (coalesced over segments);
 //   baf_grid_split_kernel one CTA per (sample, cellularity, ploidy tile, segment chunk):
 //                        the scratch rows of the CTA's next 128 segments are staged in
 //                        shared memory by TMA bulk copies (cp.async.bulk + mbarrier, one
 //                        row per copy number, two stages); every thread reads its own
-//                        16-byte entry of each row and evaluates
+//                        entry of each row and evaluates
 //                            q = (xr' * sqrt(wub))^2 + wub            (2 DFMA)
 //                            qmin = min(qmin, q)                      (DSETP + 2 FSEL)
 //                        for PT ploidies per copy number.  Running products stay in
@@ -31,7 +32,7 @@ namespace sqz {
 // ---- pre-pass: BAF factor per (column, copy number, segment) ---------------------------
 __global__ void __launch_bounds__(256)
 baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
-                   double2* __restrict__ cw) {
+                   double* __restrict__ cw) {
   extern __shared__ __align__(16) double sm[];
   double* mb = sm;            // [T] model BAF of this column (R/model.R:9-14)
   double* b_a = sm + m.T;     // [nc] model BAF at B = 0
@@ -54,7 +55,8 @@ baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
   if (s >= N_total) return;
   const double2 bk = a.bk[s];
   const double Bf = a.Bf[s];
-  double2* out = cw + (int64_t)blockIdx.y * m.nc * N_total + s;
+  const int64_t Npad = (N_total + 1) & ~(int64_t)1;  // even row pitch (16-byte aligned rows)
+  double* out = cw + (int64_t)blockIdx.y * m.nc * Npad + s;
   for (int c = 0; c < m.nc; ++c) {
     // min over B of |xb| with xb = (mb_B - Bf) kb: NaN never wins (R/bayes.R:70-72,
     // which.max skips NaN).  The model BAF is linear in B (R/model.R:10-11), so for a
@@ -76,12 +78,8 @@ baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
       }
     }
     const double u = fma(m0, m0, 1.0);  // 1 + xb^2/5
-    if (a.rp) {
-      out[(int64_t)c * N_total] = make_double2(u, 0.0);
-    } else {
-      const double wub = u * m.w[c];
-      out[(int64_t)c * N_total] = make_double2(wub, sqrt(wub));
-    }
+    // ratio.priority keeps the BAF factor apart from the ratio term (R/bayes.R:81-88)
+    out[(int64_t)c * Npad] = a.rp ? u : sqrt(u * m.w[c]);
   }
 }
 
@@ -92,27 +90,28 @@ baf_colterm_kernel(BafGridArgs a, CnModel m, int ic0, int64_t N_total,
 // stage counts the bytes; every thread then reads its own 16-byte entry of each row.
 template <int PT, bool RP, int NCT>
 __global__ void __launch_bounds__(128, 2)
-baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
-                      int nCb, int64_t N_total, double* __restrict__ partM,
+baf_grid_split_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cw, int ic0,
+                      int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
                       long long* __restrict__ partE) {
   const int nc = NCT > 0 ? NCT : m.nc;  // compile-time for the two usual ranges (0..7, 0..20)
   extern __shared__ __align__(16) double sm[];
   const int nthr = blockDim.x, tid = threadIdx.x;
+  const int nthr2 = nthr + 2;  // stage row: a run may start one segment early (alignment)
+  const int64_t Npad = (N_total + 1) & ~(int64_t)1;  // row pitch of the scratch (even)
   double* lmr = sm;                                                // [nc][PT]
-  double2* stage = reinterpret_cast<double2*>(sm + m.nc * PT);    // [2][nc][nthr]
-  int* Ec = reinterpret_cast<int*>(stage + 2 * m.nc * nthr);      // [PT][nthr]
+  double* stage = sm + m.nc * PT;                                  // [2][nc][nthr + 2]
+  int* Ec = reinterpret_cast<int*>(stage + 2 * m.nc * nthr2);     // [PT][nthr]
   __shared__ double redM[4][PT];
   __shared__ long long redE[4][PT];
   __shared__ unsigned redBad[4];
   __shared__ __align__(8) unsigned long long bar[2];
 
   int64_t b = blockIdx.x;
-  const int pt = (int)(b % a.nPT);
-  b /= a.nPT;
-  const int icl = (int)(b % nCb);
-  b /= nCb;
+  const int ub = ub0 + (int)(b % nUb);  // unit (column, tile), counted from the batch's first column
+  b /= nUb;
   const int chunk = (int)(b % a.nChunk);
   const int64_t smp = b / a.nChunk;
+  const int icl = ub / a.nPT, pt = ub - icl * a.nPT;
   const int ic = ic0 + icl;
   const int p0 = pt * PT;
   if (tid == 0) {
@@ -138,7 +137,7 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
   const int64_t cb = s0 + (int64_t)chunk * per;
   const int64_t ce = min(cb + per, s1);
-  const double2* cwc = cw + (int64_t)icl * m.nc * N_total;  // this column's scratch rows
+  const double* cwc = cw + (int64_t)icl * m.nc * Npad;  // this column's scratch rows
 
   double P[PT];
 #pragma unroll
@@ -150,11 +149,15 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
   auto issue = [&](int buf, int itn) {  // elected thread: rows of the CTA's iteration itn
     const int64_t base = cb + (int64_t)itn * nthr;
     const unsigned cnt = (unsigned)min((int64_t)nthr, ce - base);
-    mbar_expect_tx(&bar[buf], (unsigned)m.nc * cnt * (unsigned)sizeof(double2));
-    double2* dst = stage + (buf * m.nc) * nthr;
-    const double2* src = cwc + base;
-    for (int c = 0; c < nc; ++c, dst += nthr, src += N_total)
-      tma_bulk_g2s(dst, src, cnt * (unsigned)sizeof(double2), &bar[buf]);
+    // bulk copies move multiples of 16 bytes from 16-byte aligned addresses: the run starts
+    // at the even segment at or below `base` and ends at the next even count
+    const int64_t b0 = base & ~(int64_t)1;
+    const unsigned n8 = (unsigned)(((base - b0) + cnt + 1) & ~1u);
+    mbar_expect_tx(&bar[buf], (unsigned)m.nc * n8 * (unsigned)sizeof(double));
+    double* dst = stage + (buf * m.nc) * nthr2;
+    const double* src = cwc + b0;
+    for (int c = 0; c < nc; ++c, dst += nthr2, src += Npad)
+      tma_bulk_g2s(dst, src, n8 * (unsigned)sizeof(double), &bar[buf]);
   };
 
   int64_t s = cb + tid;
@@ -177,26 +180,30 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
       s = sn;
       continue;
     }
-    const double2* col = stage + (buf * m.nc) * nthr + tid;
+    // the stage holds the run that starts at the even segment at or below the CTA's first
+    const double* col = stage + (buf * m.nc) * nthr2 + (int)(cb & 1) + tid;
 
     double qmin[PT];
-    double sel[RP ? PT : 1];
+    double sel[RP ? PT : 1], q2[RP ? PT : 1];  // q2: runner-up ratio score (ratio.priority)
 #pragma unroll
     for (int j = 0; j < PT; ++j) qmin[j] = INF;
     if (RP) {
 #pragma unroll
-      for (int j = 0; j < (RP ? PT : 1); ++j) sel[j] = 1.0;
+      for (int j = 0; j < (RP ? PT : 1); ++j) {
+        sel[j] = 1.0;
+        q2[j] = INF;
+      }
     }
 #pragma unroll 2
     for (int c = 0; c < nc; ++c) {
-      const double2 cwv = col[c * nthr];
+      const double cwv = col[c * nthr2];  // sqrt(wub), or the BAF factor u with ratio.priority
       const double* l = lmr + c * PT;
       if (!RP) {
-        const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
+        const double krw = rk.x * cwv, erw = rk.y * cwv, wub = cwv * cwv;
 #pragma unroll
         for (int j = 0; j < PT; ++j) {
           const double x = fma(l[j], krw, erw);
-          const double q = fma(x, x, cwv.x);
+          const double q = fma(x, x, wub);
           if (q < qmin[j]) qmin[j] = q;  // strict <: first minimum, NaN never wins
         }
       } else {
@@ -207,11 +214,24 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
           const double x = fma(l[j], rk.x, rk.y);
           const double ar = fma(x, x, 1.0) * wc;
           if (ar < qmin[j]) {
+            q2[RP ? j : 0] = qmin[j];
             qmin[j] = ar;
-            sel[RP ? j : 0] = cwv.x;
+            sel[RP ? j : 0] = cwv;
+          } else if (ar < q2[RP ? j : 0]) {
+            q2[RP ? j : 0] = ar;
           }
         }
       }
+    }
+    if (RP) {
+      // The reference picks the copy number on dt() + log(prior) (R/bayes.R:81); here it is
+      // picked on (1 + x^2) prior^(-1/3).  When the two best are closer than rounding can
+      // tell apart, the two orders may disagree and the BAF factor of the other copy number
+      // would change the result by more than rounding: hand the grid point to the faithful
+      // kernel instead.
+#pragma unroll
+      for (int j = 0; j < (RP ? PT : 1); ++j)
+        if (q2[j] <= qmin[j] * (1.0 + 1e-12)) bad |= 1u << j;
     }
 #pragma unroll
     for (int j = 0; j < PT; ++j) P[j] *= RP ? qmin[j] * sel[RP ? j : 0] : qmin[j];
@@ -282,8 +302,8 @@ baf_grid_split_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, 
 // 0..7), which lets the bound pass unroll into independent chains held in registers.
 template <int PT, int NCT>
 __global__ void __launch_bounds__(128, 2)
-baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw, int ic0,
-                       int nCb, int64_t N_total, double* __restrict__ partM,
+baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cw, int ic0,
+                       int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
                        long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int LS = PT + 2;  // padded row stride of the log-ratio table
   constexpr bool FIX = NCT > 0;
@@ -293,21 +313,19 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   double* lmr = sm;                                                  // [nc][LS]
   double* lmid = sm + m.nc * LS;                                     // [nc] row midpoint
   double* lhw = lmid + m.nc;                                         // [nc] row half-width
-  double2* stage =
-      reinterpret_cast<double2*>(sm + m.nc * LS + 2 * ((m.nc + 1) & ~1));  // [3][nc][nthr]
-  double* LBc = reinterpret_cast<double*>(stage + 3 * m.nc * nthr);  // [nc][nthr]
+  double* stage = sm + m.nc * LS + 2 * ((m.nc + 1) & ~1);           // [3][nc][nthr]
+  double* LBc = stage + 3 * m.nc * nthr;                             // [nc][nthr]
   int* Ec = reinterpret_cast<int*>(LBc + m.nc * nthr);              // [PT][nthr]
   __shared__ double redM[4][PT];
   __shared__ long long redE[4][PT];
   __shared__ unsigned redBad[4];
 
   int64_t b = blockIdx.x;
-  const int pt = (int)(b % a.nPT);
-  b /= a.nPT;
-  const int icl = (int)(b % nCb);
-  b /= nCb;
+  const int ub = ub0 + (int)(b % nUb);  // unit (column, tile), counted from the batch's first column
+  b /= nUb;
   const int chunk = (int)(b % a.nChunk);
   const int64_t smp = b / a.nChunk;
+  const int icl = ub / a.nPT, pt = ub - icl * a.nPT;
   const int ic = ic0 + icl;
   const int p0 = pt * PT;
 
@@ -333,7 +351,8 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
   const int64_t cb = s0 + (int64_t)chunk * per;
   const int64_t ce = min(cb + per, s1);
-  const double2* cwc = cw + (int64_t)icl * m.nc * N_total;
+  const int64_t Npad = (N_total + 1) & ~(int64_t)1;  // row pitch of the scratch
+  const double* cwc = cw + (int64_t)icl * m.nc * Npad;
 
   double P[PT];
 #pragma unroll
@@ -343,10 +362,10 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
   auto issue = [&](int buf, int64_t seg) {
-    double2* dst = stage + (buf * m.nc) * nthr + tid;
-    const double2* src = cwc + seg;
+    double* dst = stage + (buf * m.nc) * nthr + tid;
+    const double* src = cwc + seg;
 #pragma unroll
-    for (int c = 0; c < nc; ++c, dst += nthr, src += N_total) cp_async16(dst, src);
+    for (int c = 0; c < nc; ++c, dst += nthr, src += Npad) cp_async8(dst, src);
     cp_async_commit();
   };
 
@@ -369,7 +388,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     if (sn + nthr < ce) issue(buf >= 1 ? buf - 1 : 2, sn + nthr);  // stage (buf + 2) % 3
     else cp_async_commit();                                        // keep the group count even
     cp_async_wait<2>();
-    const double2* col = stage + (buf * m.nc) * nthr + tid;
+    const double* col = stage + (buf * m.nc) * nthr + tid;
 
     // (a) lower bounds; the argmin only has to be a good guess, so it is taken on the
     // high words with the copy-number index packed into the low six bits
@@ -380,7 +399,7 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     for (int c = 0; c < nc; ++c) {
       double t = fabs(fma(lmid[c], rk.x, rk.y)) - lhw[c] * akr;
       if (t < 0.0) t = 0.0;
-      const double wv = col[c * nthr].x;
+      const double rv = col[c * nthr], wv = rv * rv;
       const double lb = fma(wv, t * t, wv);
       if (FIX) lbr[FIX ? c : 0] = lb;
       else LBc[c * nthr + tid] = lb;
@@ -390,13 +409,13 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
 
     double qmin[PT];
     auto eval = [&](int c) {
-      const double2 cwv = col[c * nthr];
+      const double cwv = col[c * nthr];
       const double* l = lmr + c * LS;
-      const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
+      const double krw = rk.x * cwv, erw = rk.y * cwv, wub = cwv * cwv;
 #pragma unroll
       for (int j = 0; j < PT; ++j) {
         const double x = fma(l[j], krw, erw);
-        const double q = fma(x, x, cwv.x);
+        const double q = fma(x, x, wub);
         if (q < qmin[j]) qmin[j] = q;  // strict <, NaN never wins
       }
     };
@@ -405,13 +424,13 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
     // the tile, so q = x^2 + wub peaks at one end; the larger high word plus one step of
     // 2^-20 also covers a last-place wobble of log() in the table.
     {
-      const double2 cwv = col[first * nthr];
+      const double cwv = col[first * nthr];
       const double* l = lmr + first * LS;
-      const double krw = rk.x * cwv.y, erw = rk.y * cwv.y;
+      const double krw = rk.x * cwv, erw = rk.y * cwv, wub = cwv * cwv;
 #pragma unroll
       for (int j = 0; j < PT; ++j) {
         const double x = fma(l[j], krw, erw);
-        qmin[j] = fma(x, x, cwv.x);
+        qmin[j] = fma(x, x, wub);
       }
     }
     const unsigned qh = max((unsigned)__double2hiint(qmin[0]) & 0x7FFFFFFFu,
@@ -486,40 +505,42 @@ baf_grid_pruned_kernel(BafGridArgs a, CnModel m, const double2* __restrict__ cw,
 }
 
 // ---- host side ---------------------------------------------------------------------------
+// one column of pre-pass output: [copy number][segment], rows padded to an even length
 size_t baf_split_column_bytes(int nc, int64_t N_total) {
-  return (size_t)nc * (size_t)(N_total > 0 ? N_total : 1) * sizeof(double2);
+  const size_t npad = ((size_t)(N_total > 0 ? N_total : 1) + 1) & ~(size_t)1;
+  return (size_t)nc * npad * sizeof(double);
 }
 
 static size_t split_smem_bytes(int nc, int PT, int threads) {
-  return (size_t)nc * PT * sizeof(double) + (size_t)2 * nc * threads * sizeof(double2) +
+  return (size_t)nc * PT * sizeof(double) + (size_t)2 * nc * (threads + 2) * sizeof(double) +
          (size_t)PT * threads * sizeof(int);
 }
 
 static size_t pruned_smem_bytes(int nc, int PT, int threads) {
   return (size_t)(nc * (PT + 2) + 2 * ((nc + 1) & ~1)) * sizeof(double) +
-         (size_t)3 * nc * threads * sizeof(double2) + (size_t)nc * threads * sizeof(double) +
+         (size_t)3 * nc * threads * sizeof(double) + (size_t)nc * threads * sizeof(double) +
          (size_t)PT * threads * sizeof(int);
 }
 
 template <int PT>
 static int launch_pruned(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
-                         const double2* cw, int ic0, int nCb, double* partM, long long* partE,
-                         unsigned long long* stats, cudaStream_t st) {
+                         const double* cw, int ic0, int ub0, int nUb, double* partM,
+                         long long* partE, unsigned long long* stats, cudaStream_t st) {
   const size_t smb = pruned_smem_bytes(m.nc, PT, threads);
-  const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
+  const int64_t ctas = a.S * (int64_t)nUb * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
   if (m.nc == 8) {  // CNt 0..7, what sequenza.fit always uses (R/bayes.R:40)
     SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT, 8>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     baf_grid_pruned_kernel<PT, 8><<<(unsigned)ctas, threads, smb, st>>>(
-        a, m, cw, ic0, nCb, N_total, partM, partE, stats);
+        a, m, cw, ic0, ub0, nUb, N_total, partM, partE, stats);
     SQZ_CUDA(cudaGetLastError());
     return SQZ_OK;
   }
   SQZ_CUDA(cudaFuncSetAttribute(baf_grid_pruned_kernel<PT, 0>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  baf_grid_pruned_kernel<PT, 0><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, nCb, N_total,
-                                                                     partM, partE, stats);
+  baf_grid_pruned_kernel<PT, 0><<<(unsigned)ctas, threads, smb, st>>>(a, m, cw, ic0, ub0, nUb,
+                                                                     N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
@@ -530,17 +551,17 @@ bool baf_split_supported(int nc, int PT, int threads) {
 
 template <int PT, bool RP>
 static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int64_t N_total,
-                        const double2* cw, int ic0, int nCb, double* partM, long long* partE,
-                        cudaStream_t st) {
+                        const double* cw, int ic0, int ub0, int nUb, double* partM,
+                        long long* partE, cudaStream_t st) {
   const size_t smb = split_smem_bytes(m.nc, PT, threads);
-  const int64_t ctas = a.S * (int64_t)nCb * a.nPT * a.nChunk;
+  const int64_t ctas = a.S * (int64_t)nUb * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
 #define SQZ_SPLIT_NC(NCV)                                                                   \
   do {                                                                                      \
     SQZ_CUDA(cudaFuncSetAttribute(baf_grid_split_kernel<PT, RP, NCV>,                       \
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
     baf_grid_split_kernel<PT, RP, NCV><<<(unsigned)ctas, threads, smb, st>>>(               \
-        a, m, cw, ic0, nCb, N_total, partM, partE);                                         \
+        a, m, cw, ic0, ub0, nUb, N_total, partM, partE);                                    \
   } while (0)
   if (!RP && m.nc == 21) SQZ_SPLIT_NC(21);
   else if (!RP && m.nc == 8) SQZ_SPLIT_NC(8);
@@ -550,7 +571,8 @@ static int launch_split(const BafGridArgs& a, const CnModel& m, int threads, int
   return SQZ_OK;
 }
 
-// Runs pre-pass + grid kernel over the shard's columns in batches that fit cw_bytes.
+// Runs pre-pass + grid kernel over the span's columns that hold units of this launch, in
+// batches of columns that fit cw_bytes.
 int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, int64_t N_total,
                   void* cw_buf, size_t cw_bytes, double* partM, long long* partE,
                   cudaStream_t st, bool prune, unsigned long long* stats) {
@@ -560,25 +582,32 @@ int baf_split_run(const BafGridArgs& a, const CnModel& m, int PT, int threads, i
   if (nCb_max < 1) return fail(SQZ_ERR_SIZE, "split path needs room for one column");
   if (nCb_max > a.nCs) nCb_max = a.nCs;
   if (nCb_max > 65535) nCb_max = 65535;
-  double2* cw = (double2*)cw_buf;
+  double* cw = (double*)cw_buf;
   const bool rp = a.rp != 0;
-  for (int64_t ic0 = 0; ic0 < a.nCs; ic0 += nCb_max) {
-    const int nCb = (int)((a.nCs - ic0 < nCb_max) ? (a.nCs - ic0) : nCb_max);
+  const int64_t u_end = (int64_t)a.u_first + a.nU;  // units (column, tile) of this launch
+  const int64_t c_lo = a.u_first / a.nPT, c_hi = (u_end + a.nPT - 1) / a.nPT;  // columns touched
+  for (int64_t ic0 = c_lo; ic0 < c_hi; ic0 += nCb_max) {
+    const int64_t ic1 = ic0 + nCb_max < c_hi ? ic0 + nCb_max : c_hi;
+    const int nCb = (int)(ic1 - ic0);
+    const int64_t ua = (a.u_first > ic0 * a.nPT ? a.u_first : ic0 * a.nPT) - ic0 * a.nPT;
+    const int64_t ub = (u_end < ic1 * a.nPT ? u_end : ic1 * a.nPT) - ic0 * a.nPT;
+    if (ub <= ua) continue;
+    const int ub0 = (int)ua, nUb = (int)(ub - ua);
     dim3 grid((unsigned)((N_total + 255) / 256), (unsigned)nCb);
     baf_colterm_kernel<<<grid, 256, (size_t)(m.T + 2 * m.nc) * sizeof(double), st>>>(
         a, m, (int)ic0, N_total, cw);
     SQZ_CUDA(cudaGetLastError());
     int rc;
     if (prune) {
-      if (PT == 8) rc = launch_pruned<8>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
-      else if (PT == 16) rc = launch_pruned<16>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
-      else rc = launch_pruned<32>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, stats, st);
+      if (PT == 8) rc = launch_pruned<8>(a, m, threads, N_total, cw, (int)ic0, ub0, nUb, partM, partE, stats, st);
+      else if (PT == 16) rc = launch_pruned<16>(a, m, threads, N_total, cw, (int)ic0, ub0, nUb, partM, partE, stats, st);
+      else rc = launch_pruned<32>(a, m, threads, N_total, cw, (int)ic0, ub0, nUb, partM, partE, stats, st);
       if (rc) return rc;
       continue;
     }
-#define SQZ_SPLIT(PTV)                                                                     \
-  rc = rp ? launch_split<PTV, true>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st) \
-          : launch_split<PTV, false>(a, m, threads, N_total, cw, (int)ic0, nCb, partM, partE, st)
+#define SQZ_SPLIT(PTV)                                                                          \
+  rc = rp ? launch_split<PTV, true>(a, m, threads, N_total, cw, (int)ic0, ub0, nUb, partM, partE, st) \
+          : launch_split<PTV, false>(a, m, threads, N_total, cw, (int)ic0, ub0, nUb, partM, partE, st)
     if (PT == 8) SQZ_SPLIT(8);
     else if (PT == 16) SQZ_SPLIT(16);
     else SQZ_SPLIT(32);

@@ -36,6 +36,7 @@ __device__ __forceinline__ double block_max(double v, double* red) {
   __syncthreads();
   double r = red[0];
   for (int w = 1; w < (int)(blockDim.x >> 5); ++w) r = fmax(r, red[w]);
+  __syncthreads();  // every thread has read the partials before the caller reuses `red`
   return r;
 }
 

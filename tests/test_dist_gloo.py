@@ -1,7 +1,7 @@
 """world_size-2 checks of the multi-GPU plumbing (sequenza_b200/dist.py) on CPU with the
-gloo backend: the column sharding rule and the padded all-gather that assembles
-result$LPP.  The per-rank compute is replaced by a closed-form stand-in; the kernels
-themselves are covered by the -m gpu tests."""
+gloo backend: the column and unit sharding rules, the padded all-gather of column shards
+and the one-collective assembly of unit shards.  The per-rank compute is replaced by a
+closed-form stand-in; the kernels themselves are covered by the -m gpu tests."""
 import os
 import socket
 
@@ -11,7 +11,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from sequenza_b200.dist import gather_columns, max_shard_columns, shard_columns
+from sequenza_b200.dist import (assemble_units, gather_columns, grid_plan, max_shard_columns,
+                                shard_columns, shard_units, unit_points)
 
 
 def test_shard_columns_cover_and_balance():
@@ -73,3 +74,48 @@ def test_gather_columns_world2(nC, nP, S):
     for r in range(world):
         assert not isinstance(got[r], str), got[r]
         np.testing.assert_array_equal(got[r], want)
+
+
+def _unit_worker(rank, world, port, nC, nP, S, n_seg, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        plan = grid_plan(n_seg, S, np.linspace(1, 7, nP), nC)
+        u0, u1 = shard_units(plan["units"], world, rank)
+        mine = unit_points(plan, nC, nP, u0, u1).reshape(-1)
+        # stand-in for sqz_baf_grid_dev_units: this rank's points, zeros elsewhere
+        value = -(np.arange(S)[:, None] * 1e7 + np.arange(nC * nP)[None, :] + 0.25)
+        full = torch.from_numpy(np.where(mine[None, :], value, 0.0))
+        q.put((rank, assemble_units(full).numpy(), plan["W"]))
+    except Exception as e:
+        q.put((rank, repr(e), 0))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("nC,nP,S,n_seg", [(901, 601, 1, 100000), (91, 61, 2, 3000),
+                                            (5, 3, 1, 10)])
+def test_assemble_units_world2(nC, nP, S, n_seg):
+    """Unit shards (column-per-lane units of 32 x 32 for the fine grid, (column, tile) units
+    otherwise) assembled by one all-reduce: every grid point arrives exactly once."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_unit_worker, args=(r, world, port, nC, nP, S, n_seg, q))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        r, arr, w = q.get(timeout=180)
+        got[r] = (arr, w)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = -(np.arange(S)[:, None] * 1e7 + np.arange(nC * nP)[None, :] + 0.25)
+    for r in range(world):
+        assert not isinstance(got[r][0], str), got[r][0]
+        np.testing.assert_array_equal(got[r][0], want)
+    assert got[0][1] == (32 if nC == 901 else 1)

@@ -36,3 +36,30 @@ def test_distributed_fit_single_rank():
     a = baf_model_fit_distributed(ce, pl, priors_table=PRI, **baf_args(seg))
     b = S.baf_model_fit(cellularity=ce, ploidy=pl, priors_table=PRI, **baf_args(seg))
     np.testing.assert_array_equal(a["lpp"], b["lpp"])
+
+
+def test_unit_shards_equal_host_call():
+    """sqz_baf_grid_dev_units: every world size's unit ranges, written into one whole-grid
+    buffer, reproduce the one-call result bit for bit (split, pruned and column-per-lane
+    kernels)."""
+    import torch
+    from sequenza_b200.dist import BafGridDevice, grid_plan, shard_units
+    seg = synth_segments(5000, seed=33)
+    for ce, pl, cn in ((S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1), 20),     # split
+                       (S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1), 7),      # pruned
+                       (S.r_seq(0.1, 1, 0.004), S.r_seq(1, 7, 0.02), 7)):   # column per lane
+        kw = dict(priors_table=PRI, CNt_max=cn)
+        host = S.baf_grid_sums(cellularity=ce, ploidy=pl, **kw, **baf_args(seg))
+        dev = BafGridDevice(**baf_args(seg))
+        plan = grid_plan(5000, 1, pl, ce.size, CNt_max=cn)
+        for world in (1, 3, 8):
+            buf = torch.full((1, ce.size * pl.size), float("nan"), dtype=torch.float64,
+                             device=dev.device)
+            for r in range(world):
+                u0, u1 = shard_units(plan["units"], world, r)
+                dev.run_units(pl, ce, u0, u1, out=buf, **kw)
+            np.testing.assert_array_equal(buf[0].cpu().numpy(), host)
+        # an empty range is a no-op, a range beyond the grid an error
+        dev.run_units(pl, ce, 5, 5, out=buf, **kw)
+        with pytest.raises(ValueError):
+            dev.run_units(pl, ce, 0, plan["units"] + 1, out=buf, **kw)

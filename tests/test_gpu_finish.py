@@ -88,3 +88,18 @@ def test_finish_fine_grid_and_cohort(oracle):
         np.testing.assert_allclose(f["lpp"], one["lpp"], rtol=1e-12, atol=1e-300)
         assert S.get_ci(f)["confint.cellularity"] == S.get_ci(one)["confint.cellularity"]
         assert S.get_ci(f)["confint.ploidy"] == S.get_ci(one)["confint.ploidy"]
+
+
+def test_finish_small_grid_many_samples_repeated():
+    """A 5 x 7 grid for 512 samples, 20 times: on such a small grid most threads of a CTA
+    have no grid point and race ahead -- the shape in which a missing barrier between the
+    maximum and the sum reductions would show as an occasional wrong LogSumLik."""
+    rng = np.random.default_rng(3)
+    pl, ce = np.arange(5) * 0.5 + 1.0, np.arange(7) * 0.1 + 0.2
+    sums = -500.0 + 30.0 * rng.standard_normal((512, 35))
+    want = [S.finish_model_fit(sums[k], pl, ce, device=False)["lpp"] for k in range(512)]
+    from sequenza_b200.bayes import finish_model_fit_device
+    for _ in range(20):
+        got = finish_model_fit_device(sums, pl, ce)
+        for k in range(512):
+            np.testing.assert_allclose(got[k]["lpp"], want[k], rtol=1e-12, atol=1e-300)

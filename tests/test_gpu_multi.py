@@ -1,6 +1,6 @@
 """One process driving several GPUs through the host entry points (`n_gpus` > 1): a single
-sample is cut by cellularity column, a cohort by sample.  Needs two visible devices; the
-one-GPU box skips these (tools/scale_run.sh runs them on the 8-GPU box)."""
+sample is cut into units of the grid (results stored into device 0's buffer over NVLink),
+a cohort by sample.  Needs two visible devices; the one-GPU box skips these."""
 import numpy as np
 import pytest
 
@@ -17,15 +17,20 @@ def _need_two():
         pytest.skip("needs two GPUs")
 
 
-def test_single_sample_column_shards():
+@pytest.mark.parametrize("n_seg,grid,cn_max", [(4000, (0.01, 0.1), 7), (4000, (0.01, 0.1), 20),
+                                               (20000, (0.002, 0.02), 7)])
+def test_single_sample_unit_shards_are_bit_identical(n_seg, grid, cn_max):
+    """The bits of a grid point do not depend on the number of GPUs (the kernel, its tiles
+    and its segment chunks are planned from the whole grid)."""
     _need_two()
-    seg = synth_segments(4000, seed=71)
-    ce, pl = S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1)
-    one = S.baf_grid_sums(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=1, **baf_args(seg))
-    for n in (2, _lib.lib().sqz_device_count()):
-        many = S.baf_grid_sums(cellularity=ce, ploidy=pl, priors_table=PRI, n_gpus=n,
-                               **baf_args(seg))
-        np.testing.assert_allclose(many, one, rtol=1e-12, atol=0)
+    seg = synth_segments(n_seg, seed=71)
+    ce, pl = S.r_seq(0.1, 1, grid[0]), S.r_seq(1, 7, grid[1])
+    kw = dict(cellularity=ce, ploidy=pl, priors_table=PRI, CNt_max=cn_max, **baf_args(seg))
+    one = S.baf_grid_sums(n_gpus=1, **kw)
+    for n in sorted({2, _lib.lib().sqz_device_count()}):
+        for _ in range(2):  # the second call reuses the cached buffers
+            many = S.baf_grid_sums(n_gpus=n, **kw)
+            np.testing.assert_array_equal(many, one)
 
 
 @pytest.mark.parametrize("sizes", [[300, 0, 1200, 50, 700], [1] * 9, [0, 0, 40], [2500] * 16])

@@ -19,10 +19,11 @@ RTOL = 1e-9  # the LPP tolerance of the other GPU parity tests
 PRI = {"CN": [2], "value": [2]}
 
 
-def test_noalloc_matches_workspace_entry_point_twice_in_a_row():
+def test_noalloc_matches_workspace_entry_point_twice_in_a_row(oracle):
     """Two consecutive calls on different inputs and sizes (the second is smaller, so
     anything the first call left in the shared scratch would show up) against the
-    existing workspace-taking entry point, through the C ABI."""
+    existing workspace-taking entry point, through the C ABI -- and, as the third leg,
+    against the CPU oracle on a window of grid points around the fitted solution."""
     import torch
     from sequenza_b200.dist import BafGridDevice, run_noalloc
     ce, pl = S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1)
@@ -42,6 +43,12 @@ def test_noalloc_matches_workspace_entry_point_twice_in_a_row():
         assert np.isfinite(b).all()
         np.testing.assert_allclose(a, b, rtol=RTOL, atol=0)
         assert int(np.argmax(a)) == int(np.argmax(b))
+        k = int(np.argmax(a))
+        g0 = max(0, min(k - 32, a.size - 64))
+        ref = oracle.baf_grid_sums(cellularity=ce, ploidy=pl, g0=g0, g1=g0 + 64,
+                                   **baf_args(seg), **kw)
+        np.testing.assert_allclose(a[g0:g0 + 64], ref, rtol=RTOL, atol=0)
+        assert g0 + int(np.argmax(ref)) == k
     # a column shard, and a degenerate input that goes through the repair kernel
     seg = synth_segments(300, seed=63)
     seg["sd_ratio"][5] = 0.0
