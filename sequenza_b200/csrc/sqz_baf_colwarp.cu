@@ -18,9 +18,15 @@
 //             nothing is shared between them and the hardware scheduler balances them;
 //             the tiles of one (group, chunk) are neighbours in the grid and find each
 //             other's rows in L2.
-//   ring      kRing stages of kSegB segments; lane 0 fills a stage with one TMA bulk copy
+//   ring      two stages of cw_batch() segments; lane 0 fills a stage with one TMA bulk copy
 //             (plus one for the segments' ratio terms) and completion is counted on an
 //             mbarrier; the stage is refilled as soon as the warp has left it.
+//   batch     the segments of a stage are analysed together (bounds, argmin, dynamic loads,
+//             warp vote: a serial chain per segment, independent between segments; results
+//             parked in shared memory), then evaluated one after the other by ONE copy of
+//             the evaluation code (long runs of independent DFMA/DMUL; the kernel has to
+//             stay small: with every warp at a different place, a larger body stalls on
+//             instruction fetch).
 //   thread    = one (column, tile): the tile's -log(ploidy term) centred on its midpoint in
 //             registers, running products in registers, exponents in shared memory
 //
@@ -31,6 +37,8 @@
 // Candidate rule as in baf_grid_pruned_kernel.  The warp-uniform number of extra candidates
 // (0 in 3/4 of the iterations, 1 in 1/5) selects the loop: the minimum over candidates is
 // taken ploidy by ploidy, so no array of minima is kept next to the products.
+#include <type_traits>
+
 #include "sqz_async.cuh"
 #include "sqz_baf_grid.cuh"
 #include "../../include/sequenza_b200.h"
@@ -38,7 +46,9 @@
 namespace sqz {
 
 namespace {
-constexpr int kRing = 3;   // stages: two in flight while one is consumed
+// Segments per stage of the ring = segments whose analyses run together (their serial
+// chains overlap in one basic block).  Two stages: one is worked on, the other in flight.
+__host__ __device__ constexpr int cw_batch(int nc) { return nc <= 8 ? 4 : 1; }
 constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 }  // namespace
 
@@ -100,22 +110,31 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
 }
 
 // ---- grid kernel -------------------------------------------------------------------------
+// What the analysis of one segment leaves for its evaluation, per lane, in shared memory:
+//   three doubles  k1, b1, w1: first candidate, x_j = fma(nld_j, k1, b1), q_j = fma(x_j, x_j, w1)
+//   word 0         further copy numbers this lane cannot exclude | first candidate << 24
+//                  (a lane without a further one repeats its first)
+//   word 1         upper bound of the binary exponent the products gain | (the longest
+//                  candidate list in the warp, warp-uniform) << 16
+
 template <int PT, int NC>
 __global__ void __launch_bounds__(32, 8)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
                         int nCb, int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
                         long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int kSegDoubles = NC * 32;  // one segment of a column group
-  constexpr int kSegB = NC <= 8 ? 2 : 1;  // segments per stage (a stage is at most 5.25 KB)
-  constexpr bool SQ = NC <= 8;            // the scratch holds sqrt(wub) (else wub)
+  constexpr int kSegB = cw_batch(NC);   // segments per stage = segments analysed together
+  constexpr int kRing = 2;              // one stage is worked on while the other is in flight
+  constexpr bool SQ = NC <= 8;          // the scratch holds sqrt(wub) (else wub)
   constexpr int nthr = 32;
   extern __shared__ __align__(16) double sm[];
   const int lane = threadIdx.x, tid = threadIdx.x;
-  double* stage = sm;                                                               // [kRing][kSegB][NC][32]
+  double* stage = sm;                                                           // [kRing][kSegB][NC][32]
   double2* rkS = reinterpret_cast<double2*>(stage + kRing * kSegB * kSegDoubles);  // [kRing][kSegB]
-  double* lm = reinterpret_cast<double*>(rkS + kRing * kSegB) + lane;              // [NC][32]
-  double* qS = lm - lane + NC * 32;                                                 // [PT][32] (rare path)
-  int* Ec = reinterpret_cast<int*>(qS + PT * 32);                                   // [PT][32]
+  double* lm = reinterpret_cast<double*>(rkS + kRing * kSegB) + lane;          // [NC][32]
+  int* Ec = reinterpret_cast<int*>(lm - lane + NC * 32);                        // [PT][32]
+  double* pk = reinterpret_cast<double*>(Ec + PT * 32) + lane;                  // [kSegB][3][32]
+  unsigned* pw = reinterpret_cast<unsigned*>(pk - lane + kSegB * 3 * 32) + lane;  // [kSegB][2][32]
   __shared__ __align__(8) unsigned long long full[kRing];
 
   // CTA -> (unit of this launch, chunk, sample); units run tile-fastest inside a column
@@ -163,9 +182,9 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const int64_t ce = min(cb + per, s1);
   const double* cwc = cwg + (int64_t)cg * N_total * kSegDoubles;  // this group's rows
 
-  // Requests run ahead of the consumption by kRing - 1 blocks; the state below is
-  // warp-uniform, lane 0 issues.  A stage is requested again only after every lane has
-  // left it (the __syncwarp before the call).
+  // Requests run one stage ahead of the consumption; the state below is warp-uniform, lane
+  // 0 issues.  A stage is requested again only after every lane has left it (the
+  // __syncwarp before the call).
   const double* f_src = cwc + cb * kSegDoubles;
   const double2* f_rk = a.rk + cb;
   int64_t f_left = ce - cb;  // segments not yet requested
@@ -182,7 +201,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     f_src += kSegB * kSegDoubles;
     f_rk += kSegB;
     f_left -= kSegB;
-    f_s = f_s == kRing - 1 ? 0 : f_s + 1;
+    f_s ^= 1;
   };
 
   double P[PT];
@@ -193,123 +212,213 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // renormalisation: every factor is at most the first candidate's q at a tile end.
   int grown = 0;
 
-  for (int k = 0; k < kRing - 1; ++k) fetch();
-  int s = 0;
-  unsigned phase = 0;
-  for (int64_t left = ce - cb; left > 0; left -= kSegB) {
-    __syncwarp();
-    fetch();
-    mbar_wait(&full[s], phase);
-    const int nsg = left < kSegB ? (int)left : kSegB;
-#pragma unroll 1
-    for (int sg = 0; sg < nsg; ++sg) {
-      const double2 rk = rkS[s * kSegB + sg];
-      const double* col = stage + (s * kSegB + sg) * kSegDoubles + lane;  // stored value of c: [c * 32]
-
-      // (a) lower bound of every copy number over the tile (high words are enough: Qmax
-      // below has a zero low word); argmin on the high words with the index packed in.
-      // max(t0, 0) = t0/2 + |t0/2| with exact halves: one DADD, no compare and selects.
-      const double hx = 0.5 * rk.x, hy = 0.5 * rk.y;
-      const double ah = hw * fabs(hx);
-      unsigned lbh[NC];
-      unsigned kbest = 0xFFFFFFFFu;
+  // ---- analysis of one segment: which copy numbers have to be evaluated ------------------
+  // A serial chain (bounds -> argmin -> dynamic loads -> Qmax -> candidate mask -> warp
+  // vote).  The segments of a stage are analysed together, in one basic block, so that
+  // their chains overlap; the evaluations (long runs of independent DFMA/DMUL) follow.
+  // B segments at once, written phase by phase ACROSS the segments (all bound passes, all
+  // argmins, all dynamic loads, ...): the hardware issues a warp's instructions in order, so
+  // independent chains overlap only if they are interleaved in the instruction stream.  The
+  // warp votes and the stores come last: a warp-synchronous operation or a shared-memory
+  // store in the middle would pin the order.
+  auto analyse = [&](int base, auto bt) {
+    constexpr int B = decltype(bt)::value;
+    double2 rk[B];
+    const double* col[B];
+    unsigned lbh[B][NC], kbest[B];
 #pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        const double t0 = fabs(fma(lm[c * 32], hx, hy)) - ah;
+    for (int g = 0; g < B; ++g) {
+      rk[g] = rkS[base + g];
+      col[g] = stage + (base + g) * kSegDoubles + lane;  // stored value of c: [c * 32]
+      kbest[g] = 0xFFFFFFFFu;
+    }
+    // (a) lower bound of every copy number over the tile (high words are enough: Qmax
+    // below has a zero low word); argmin on the high words with the index packed in.
+    // max(t0, 0) = t0/2 + |t0/2| with exact halves: one DADD, no compare and selects.
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const double lmc = lm[c * 32];
+#pragma unroll
+      for (int g = 0; g < B; ++g) {
+        const double hx = 0.5 * rk[g].x, hy = 0.5 * rk[g].y;
+        const double t0 = fabs(fma(lmc, hx, hy)) - hw * fabs(hx);
         const double t = t0 + fabs(t0);
-        const double rv = col[c * 32], u = SQ ? rv * t : t * t;
-        lbh[c] = (unsigned)__double2hiint(SQ ? fma(u, u, rv * rv) : fma(rv, u, rv));
-        kbest = min(kbest, (lbh[c] & 0xFFFFFFC0u) | (unsigned)c);
+        const double rv = col[g][c * 32], u = SQ ? rv * t : t * t;
+        lbh[g][c] = (unsigned)__double2hiint(SQ ? fma(u, u, rv * rv) : fma(rv, u, rv));
+        kbest[g] = min(kbest[g], (lbh[g][c] & 0xFFFFFFC0u) | (unsigned)c);
       }
-      const int first = (int)(kbest & 63u) < NC ? (int)(kbest & 63u) : 0;
-
-      // (b) the most promising copy number; (c) Qmax from the two ends of the tile
-      const double v1 = col[first * 32];
-      const double r1 = SQ ? v1 : sqrt(v1), w1 = SQ ? v1 * v1 : v1;
-      const double k1 = rk.x * r1;
-      const double b1 = fma(lm[first * 32], k1, rk.y * r1);
-      const double xa = fma(nld[0], k1, b1), xb = fma(nld[PT - 1], k1, b1);
-      const unsigned qh = max((unsigned)__double2hiint(fma(xa, xa, w1)) & 0x7FFFFFFFu,
-                              (unsigned)__double2hiint(fma(xb, xb, w1)) & 0x7FFFFFFFu);
-      // (d) copy numbers that can still lower a minimum: lb < Qmax = (qh + 1, 0), i.e. the
-      // high word of lb is at most qh; Qmax = +Inf keeps every finite bound
-      const unsigned qcap = qh >= 0x7FF00000u ? 0x7FEFFFFFu : qh;
-      grown += (int)(qh >> 20) - 1021;
-      unsigned need = 0;
+    }
+    // (b) the most promising copy number
+    int first[B];
+    double v1[B], lf[B];
+#pragma unroll
+    for (int g = 0; g < B; ++g) {
+      first[g] = (int)(kbest[g] & 63u) < NC ? (int)(kbest[g] & 63u) : 0;
+      v1[g] = col[g][first[g] * 32];
+      lf[g] = lm[first[g] * 32];
+    }
+    double k1[B], b1[B], w1[B];
+#pragma unroll
+    for (int g = 0; g < B; ++g) {
+      const double r1 = SQ ? v1[g] : sqrt(v1[g]);
+      w1[g] = SQ ? v1[g] * v1[g] : v1[g];
+      k1[g] = rk[g].x * r1;
+      b1[g] = fma(lf[g], k1[g], rk[g].y * r1);
+    }
+    // (c) Qmax from the two ends of the tile
+    unsigned qh[B];
+#pragma unroll
+    for (int g = 0; g < B; ++g) {
+      const double xa = fma(nld[0], k1[g], b1[g]), xb = fma(nld[PT - 1], k1[g], b1[g]);
+      qh[g] = max((unsigned)__double2hiint(fma(xa, xa, w1[g])) & 0x7FFFFFFFu,
+                  (unsigned)__double2hiint(fma(xb, xb, w1[g])) & 0x7FFFFFFFu);
+    }
+    // (d) copy numbers that can still lower a minimum: lb < Qmax = (qh + 1, 0), i.e. the
+    // high word of lb is at most qh; Qmax = +Inf keeps every finite bound
+    unsigned need[B];
+#pragma unroll
+    for (int g = 0; g < B; ++g) {
+      const unsigned qcap = qh[g] >= 0x7FF00000u ? 0x7FEFFFFFu : qh[g];
+      need[g] = 0;
 #pragma unroll
       for (int c = 0; c < NC; ++c)
-        if (lbh[c] <= qcap) need |= 1u << c;
-      need &= ~(1u << first);
-      const unsigned nx = (unsigned)__popc(need);
-      const unsigned nmax = __reduce_max_sync(0xffffffffu, nx);
-      n_eval += 1u + nmax;  // what the warp executes: every lane follows the longest list
+        if (lbh[g][c] <= qcap) need[g] |= 1u << c;
+      need[g] &= ~(1u << first[g]);
+    }
+    unsigned nmax[B];
+#pragma unroll
+    for (int g = 0; g < B; ++g) nmax[g] = __reduce_max_sync(0xffffffffu, (unsigned)__popc(need[g]));
+#pragma unroll
+    for (int g = 0; g < B; ++g) {
+      pk[(g * 3 + 0) * 32] = k1[g];
+      pk[(g * 3 + 1) * 32] = b1[g];
+      pk[(g * 3 + 2) * 32] = w1[g];
+      pw[(g * 2 + 0) * 32] = need[g] | ((unsigned)first[g] << 24);
+      pw[(g * 2 + 1) * 32] = (qh[g] >> 20) | (nmax[g] << 16);  // exponent field: at most 0x7FF
+    }
+  };
 
-      if (nmax == 0) {
+  // ---- evaluation of one analysed segment: the products take in its minimum ----------------
+  auto evaluate = [&](int slot, int idx) {
+    struct {
+      double k1, b1, w1;
+      unsigned need, nmax;
+      int first, gr;
+    } sg;
+    sg.k1 = pk[(idx * 3 + 0) * 32];
+    sg.b1 = pk[(idx * 3 + 1) * 32];
+    sg.w1 = pk[(idx * 3 + 2) * 32];
+    {
+      const unsigned w0 = pw[(idx * 2 + 0) * 32], w1 = pw[(idx * 2 + 1) * 32];
+      sg.need = w0 & 0x00FFFFFFu;
+      sg.first = (int)(w0 >> 24);
+      sg.gr = (int)(w1 & 0xFFFFu) - 1021;
+      sg.nmax = w1 >> 16;
+    }
+    if (sg.nmax == 0) {
+      // common case (3 of 4): the first candidate alone; no minimum to take
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const double x = fma(nld[j], sg.k1, sg.b1);
+        P[j] *= fma(x, x, sg.w1);
+      }
+    } else {
+      const double2 rk = rkS[slot];
+      const double* col = stage + slot * kSegDoubles + lane;
+      unsigned need = sg.need;
+      // a lane with no further candidate repeats its first one: the minimum is unchanged
+      const int c2 = need ? __ffs((int)need) - 1 : sg.first;
+      need &= need - 1;
+      const double v2 = col[c2 * 32];
+      const double r2 = SQ ? v2 : sqrt(v2), w2 = SQ ? v2 * v2 : v2;
+      const double k2 = rk.x * r2;
+      const double b2 = fma(lm[c2 * 32], k2, rk.y * r2);
+      if (sg.nmax == 1) {
 #pragma unroll
         for (int j = 0; j < PT; ++j) {
-          const double x = fma(nld[j], k1, b1);
-          P[j] *= fma(x, x, w1);
+          const double x = fma(nld[j], sg.k1, sg.b1), y = fma(nld[j], k2, b2);
+          double q = fma(x, x, sg.w1);
+          const double q2 = fma(y, y, w2);
+          if (q2 < q) q = q2;  // strict <: a NaN in the first stays and is flagged
+          P[j] *= q;
         }
       } else {
-        // a lane with no further candidate repeats its first one: the minimum is unchanged
-        int c2 = need ? __ffs((int)need) - 1 : first;
-        need &= need - 1;
-        double v2 = col[c2 * 32];
-        double r2 = SQ ? v2 : sqrt(v2), w2 = SQ ? v2 * v2 : v2;
-        double k2 = rk.x * r2;
-        double b2 = fma(lm[c2 * 32], k2, rk.y * r2);
-        if (nmax == 1) {
+        // rare (1 in 20): several further candidates.  Eight ploidies at a time keep the
+        // minima in registers; the candidate list is walked again for every block.
 #pragma unroll
-          for (int j = 0; j < PT; ++j) {
-            const double x = fma(nld[j], k1, b1), y = fma(nld[j], k2, b2);
-            double q = fma(x, x, w1);
+        for (int jb = 0; jb < PT; jb += 8) {
+          double q[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const double x = fma(nld[jb + j], sg.k1, sg.b1), y = fma(nld[jb + j], k2, b2);
+            q[j] = fma(x, x, sg.w1);
             const double q2 = fma(y, y, w2);
-            if (q2 < q) q = q2;  // strict <: a NaN in the first stays and is flagged
-            P[j] *= q;
+            if (q2 < q[j]) q[j] = q2;
           }
-        } else {
-          double* qs = qS + tid;  // [j * nthr]
+          unsigned nd = need;
+          for (unsigned k = 2; k <= sg.nmax; ++k) {
+            const int c3 = nd ? __ffs((int)nd) - 1 : sg.first;
+            nd &= nd - 1;
+            const double v3 = col[c3 * 32];
+            const double r3 = SQ ? v3 : sqrt(v3), w3 = SQ ? v3 * v3 : v3;
+            const double k3 = rk.x * r3;
+            const double b3 = fma(lm[c3 * 32], k3, rk.y * r3);
 #pragma unroll
-          for (int j = 0; j < PT; ++j) {
-            const double x = fma(nld[j], k1, b1), y = fma(nld[j], k2, b2);
-            double q = fma(x, x, w1);
-            const double q2 = fma(y, y, w2);
-            if (q2 < q) q = q2;
-            qs[j * nthr] = q;
-          }
-          for (unsigned k = 2; k <= nmax; ++k) {
-            c2 = need ? __ffs((int)need) - 1 : first;
-            need &= need - 1;
-            v2 = col[c2 * 32];
-            r2 = SQ ? v2 : sqrt(v2);
-            w2 = SQ ? v2 * v2 : v2;
-            k2 = rk.x * r2;
-            b2 = fma(lm[c2 * 32], k2, rk.y * r2);
-#pragma unroll
-            for (int j = 0; j < PT; ++j) {
-              const double y = fma(nld[j], k2, b2);
-              const double q2 = fma(y, y, w2);
-              if (q2 < qs[j * nthr]) qs[j * nthr] = q2;
+            for (int j = 0; j < 8; ++j) {
+              const double y = fma(nld[jb + j], k3, b3);
+              const double q3 = fma(y, y, w3);
+              if (q3 < q[j]) q[j] = q3;
             }
           }
 #pragma unroll
-          for (int j = 0; j < PT; ++j) P[j] *= qs[j * nthr];
-        }
-      }
-
-      // the products are renormalised (binary exponent -> integer column) before they can
-      // overflow; q >= 1, so they never underflow
-      if (__any_sync(0xffffffffu, grown > 900)) {
-        grown = 0;
-#pragma unroll
-        for (int j = 0; j < PT; ++j) {
-          const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
-          if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
-          Ec[j * nthr + tid] += (hi >> 20) - 1023;
-          P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+          for (int j = 0; j < 8; ++j) P[jb + j] *= q[j];
         }
       }
     }
+    n_eval += 1u + sg.nmax;  // what the warp executes: every lane follows the longest list
+    grown += sg.gr;
+    // the products are renormalised (binary exponent -> integer column) before they can
+    // overflow; q >= 1, so they never underflow
+    if (__any_sync(0xffffffffu, grown > 900)) {
+      grown = 0;
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+        if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+        Ec[j * nthr + tid] += (hi >> 20) - 1023;
+        P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+      }
+    }
+  };
+
+  fetch();
+  int s = 0;
+  unsigned phase = 0;
+#pragma unroll 1
+  for (int64_t left = ce - cb; left > 0; left -= kSegB) {
+    __syncwarp();
+    fetch();  // the stage left in the previous round is requested again
+    mbar_wait(&full[s], phase);
+    const int base = s * kSegB;
+    const int nsg = left < kSegB ? (int)left : kSegB;
+    if (nsg == kSegB) {
+      analyse(base, std::integral_constant<int, kSegB>());
+    } else if (nsg >= 2 && kSegB > 2) {  // ragged last stage of the chunk
+      analyse(base, std::integral_constant<int, 2>());
+      if (nsg == 3) {
+        // the third segment's results go to slot 2: shift the parking position
+        pk += 2 * 3 * 32;
+        pw += 2 * 2 * 32;
+        analyse(base + 2, std::integral_constant<int, 1>());
+        pk -= 2 * 3 * 32;
+        pw -= 2 * 2 * 32;
+      }
+    } else {
+      analyse(base, std::integral_constant<int, 1>());
+    }
+    // (each lane reads back only what it wrote itself: no warp synchronisation needed)
+#pragma unroll 1
+    for (int sg = 0; sg < nsg; ++sg) evaluate(base + sg, sg);
     if (++s == kRing) {
       s = 0;
       phase ^= 1u;
@@ -338,10 +447,10 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 
 // ---- host side ---------------------------------------------------------------------------
 static size_t colwarp_smem_bytes(int NC, int PT) {
-  const int segb = NC <= 8 ? 2 : 1;
-  return (size_t)kRing * segb * NC * 32 * sizeof(double) + kRing * segb * sizeof(double2) +
-         (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(double) +
-         (size_t)PT * 32 * sizeof(int);
+  const int segb = cw_batch(NC), ring = 2;
+  return (size_t)ring * segb * NC * 32 * sizeof(double) + ring * segb * sizeof(double2) +
+         (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(int) +
+         (size_t)segb * 32 * (3 * sizeof(double) + 2 * sizeof(unsigned));
 }
 
 static size_t colterm_cg_smem_bytes(int nc, int T) {
