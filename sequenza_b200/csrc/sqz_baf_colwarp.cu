@@ -37,6 +37,8 @@
 // Candidate rule as in baf_grid_pruned_kernel.  The warp-uniform number of extra candidates
 // (0 in 3/4 of the iterations, 1 in 1/5) selects the loop: the minimum over candidates is
 // taken ploidy by ploidy, so no array of minima is kept next to the products.
+#include <stdlib.h>
+
 #include <type_traits>
 
 #include "sqz_async.cuh"
@@ -117,13 +119,13 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
 //   word 1         upper bound of the binary exponent the products gain | (the longest
 //                  candidate list in the warp, warp-uniform) << 16
 
-template <int PT, int NC>
-__global__ void __launch_bounds__(32, 8)
+template <int PT, int NC, int SB, int OCC>
+__global__ void __launch_bounds__(32, OCC)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
                         int nCb, int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
                         long long* __restrict__ partE, unsigned long long* __restrict__ stats) {
   constexpr int kSegDoubles = NC * 32;  // one segment of a column group
-  constexpr int kSegB = cw_batch(NC);   // segments per stage = segments analysed together
+  constexpr int kSegB = SB;             // segments per stage = segments analysed together
   constexpr int kRing = 2;              // one stage is worked on while the other is in flight
   constexpr bool SQ = NC <= 8;          // the scratch holds sqrt(wub) (else wub)
   constexpr int nthr = 32;
@@ -299,22 +301,24 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   };
 
   // ---- evaluation of one analysed segment: the products take in its minimum ----------------
-  auto evaluate = [&](int slot, int idx) {
-    struct {
-      double k1, b1, w1;
-      unsigned need, nmax;
-      int first, gr;
-    } sg;
+  struct CwPar {
+    double k1, b1, w1;
+    unsigned need, nmax;
+    int first, gr;
+  };
+  auto load_par = [&](int idx) {
+    CwPar sg;
     sg.k1 = pk[(idx * 3 + 0) * 32];
     sg.b1 = pk[(idx * 3 + 1) * 32];
     sg.w1 = pk[(idx * 3 + 2) * 32];
-    {
-      const unsigned w0 = pw[(idx * 2 + 0) * 32], w1 = pw[(idx * 2 + 1) * 32];
-      sg.need = w0 & 0x00FFFFFFu;
-      sg.first = (int)(w0 >> 24);
-      sg.gr = (int)(w1 & 0xFFFFu) - 1021;
-      sg.nmax = w1 >> 16;
-    }
+    const unsigned w0 = pw[(idx * 2 + 0) * 32], w1 = pw[(idx * 2 + 1) * 32];
+    sg.need = w0 & 0x00FFFFFFu;
+    sg.first = (int)(w0 >> 24);
+    sg.gr = (int)(w1 & 0xFFFFu) - 1021;
+    sg.nmax = w1 >> 16;
+    return sg;
+  };
+  auto evaluate = [&](int slot, const CwPar& sg) {
     if (sg.nmax == 0) {
       // common case (3 of 4): the first candidate alone; no minimum to take
 #pragma unroll
@@ -377,18 +381,6 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     }
     n_eval += 1u + sg.nmax;  // what the warp executes: every lane follows the longest list
     grown += sg.gr;
-    // the products are renormalised (binary exponent -> integer column) before they can
-    // overflow; q >= 1, so they never underflow
-    if (__any_sync(0xffffffffu, grown > 900)) {
-      grown = 0;
-#pragma unroll
-      for (int j = 0; j < PT; ++j) {
-        const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
-        if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
-        Ec[j * nthr + tid] += (hi >> 20) - 1023;
-        P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
-      }
-    }
   };
 
   fetch();
@@ -416,9 +408,31 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     } else {
       analyse(base, std::integral_constant<int, 1>());
     }
-    // (each lane reads back only what it wrote itself: no warp synchronisation needed)
+    // (each lane reads back only what it wrote itself: no warp synchronisation needed);
+    // the parameters of the next segment are loaded while the current one is evaluated
+    {
+      CwPar cur = load_par(0);
 #pragma unroll 1
-    for (int sg = 0; sg < nsg; ++sg) evaluate(base + sg, sg);
+      for (int sg = 0; sg < nsg; ++sg) {
+        const CwPar nxt = load_par(sg + 1 < nsg ? sg + 1 : sg);
+        evaluate(base + sg, cur);
+        cur = nxt;
+      }
+    }
+    // Once per stage: the products are renormalised (binary exponent -> integer column)
+    // before they can overflow; q >= 1, so they never underflow.  `grown` bounds the
+    // exponent gained since the last time; a stage that gains more than 2^300 on its own
+    // overflows to Inf, which is flagged and repaired like any other non-finite product.
+    if (__any_sync(0xffffffffu, grown > 700)) {
+      grown = 0;
+#pragma unroll
+      for (int j = 0; j < PT; ++j) {
+        const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+        if ((unsigned)(hi - 0x00100000) >= 0x7FE00000u) bad |= 1u << j;
+        Ec[j * nthr + tid] += (hi >> 20) - 1023;
+        P[j] = __hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo);
+      }
+    }
     if (++s == kRing) {
       s = 0;
       phase ^= 1u;
@@ -446,8 +460,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 }
 
 // ---- host side ---------------------------------------------------------------------------
-static size_t colwarp_smem_bytes(int NC, int PT) {
-  const int segb = cw_batch(NC), ring = 2;
+static size_t colwarp_smem_bytes(int NC, int PT, int segb) {
+  const int ring = 2;
   return (size_t)ring * segb * NC * 32 * sizeof(double) + ring * segb * sizeof(double2) +
          (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(int) +
          (size_t)segb * 32 * (3 * sizeof(double) + 2 * sizeof(unsigned));
@@ -470,18 +484,18 @@ size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
   return (size_t)nc * 32 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
 }
 
-template <int PT, int NC>
+template <int PT, int NC, int SB, int OCC>
 static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_total,
                           const double* cwg, int ic0, int nCb, int ub0, int nUb, double* partM,
                           long long* partE, unsigned long long* stats, cudaStream_t st) {
   const int64_t ctas = a.S * (int64_t)nUb * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  const size_t smb = colwarp_smem_bytes(NC, PT);
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
+  const size_t smb = colwarp_smem_bytes(NC, PT, SB);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC>,
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC>,
                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-  baf_grid_colwarp_kernel<PT, NC><<<(unsigned)ctas, 32, smb, st>>>(
+  baf_grid_colwarp_kernel<PT, NC, SB, OCC><<<(unsigned)ctas, 32, smb, st>>>(
       a, m, cwg, ic0, nCb, ub0, nUb, N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
@@ -516,15 +530,19 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
                                                        m.nc <= 8 ? 1 : 0, cwg);
     SQZ_CUDA(cudaGetLastError());
     int rc;
-#define SQZ_CW(PTV, NCV)                                                                  \
-  rc = launch_colwarp<PTV, NCV>(a, m, N_total, cwg, (int)ic0, nCb, (int)ua, (int)(ub - ua), \
-                                partM, partE, stats, st)
+#define SQZ_CW(PTV, NCV, SBV, OCCV)                                                       \
+  rc = launch_colwarp<PTV, NCV, SBV, OCCV>(a, m, N_total, cwg, (int)ic0, nCb, (int)ua,    \
+                                           (int)(ub - ua), partM, partE, stats, st)
+    const char* var_env = getenv("SQZ_CW_VARIANT");  // experiments only
+    const int variant = var_env ? atoi(var_env) : 0;
     if (m.nc == 8) {
-      if (PT == 16) SQZ_CW(16, 8);
-      else SQZ_CW(32, 8);
+      if (PT == 16) SQZ_CW(16, 8, cw_batch(8), 8);
+      else if (variant == 1) SQZ_CW(32, 8, 2, 12);
+      else if (variant == 2) SQZ_CW(32, 8, 2, 8);
+      else SQZ_CW(32, 8, cw_batch(8), 8);
     } else {
-      if (PT == 16) SQZ_CW(16, 21);
-      else SQZ_CW(32, 21);
+      if (PT == 16) SQZ_CW(16, 21, cw_batch(21), 8);
+      else SQZ_CW(32, 21, cw_batch(21), 8);
     }
 #undef SQZ_CW
     if (rc) return rc;
