@@ -1,7 +1,8 @@
 # Replacement bodies for the four functions of R/bayes.R that sit on the likelihood
-# path, plus sequenza.fit's optional CNt.max pass-through.  Signatures, defaults and
-# return values are the reference's; only the work between the argument recycling and
-# the result assembly moves to the GPU.  UNTESTED HERE (no R in the build image).
+# path (the CNt.max / n.gpus pass-through of sequenza.fit is a patch: see the end of this
+# file).  Signatures, defaults and return values are the reference's; only the work
+# between the argument recycling and the result assembly moves to the GPU.
+# UNTESTED HERE (no R in the build image).
 #
 # NAMESPACE: add   useDynLib(sequenza, .registration = TRUE)
 # DESCRIPTION: set NeedsCompilation: yes
@@ -75,7 +76,7 @@ mufreq.bayes <- function(mufreq, depth.ratio, cellularity,
     if (length(weight.mufreq) == 1 && length(weight.ratio) == 1 &&
         weight.mufreq == round(weight.mufreq) && weight.ratio == round(weight.ratio) &&
         weight.mufreq >= 0 && weight.ratio >= 0 && weight.mufreq <= 4096 &&
-        weight.ratio <= 4096) {
+        weight.ratio <= 4096 && (weight.mufreq + 1) * (weight.ratio + 1) <= 4e6) {
         # scalar weights (the defaults; R/results.R:153-157): table-driven kernel
         mufreq.tab <- data.frame(F = mufreq, ratio = depth.ratio)
         types.L <- .Call(sqzr_mufreq_point_scalar, as.double(mufreq.tab$F),
@@ -116,9 +117,11 @@ mufreq.model.fit <- function(cellularity = seq(0.3, 1, by = 0.01),
     .sqz.finish(result)
 }
 
-# sequenza.fit (R/fit.R:1-69) is unchanged except for two optional arguments at the end
-# of its signature, forwarded to baf.model.fit at R/fit.R:45-50:
+# sequenza.fit (R/fit.R:1-69): two optional arguments at the end of its signature,
 #     CNt.max = 7, n.gpus = getOption("sequenza.gpus", 1L)
-# (the reference cannot reach CNt.max = 20 from sequenza.fit; defaults keep its result.)
+# forwarded to baf.model.fit (R/fit.R:45-50) and mufreq.model.fit (R/fit.R:61-65).  The edit
+# is r-package/patches/sequenza-3.0.0-gpu.patch (apply with `patch -p1` in the package
+# root; it also adds useDynLib to NAMESPACE and sets NeedsCompilation in DESCRIPTION).
+# The reference cannot reach CNt.max = 20 from sequenza.fit; the defaults keep its result.
 # get.ci / alternative.cp.solutions (R/solutions.R) and sequenza.results (R/results.R)
 # need no change: they consume list(ploidy, cellularity, lpp) and the N x 4 matrices.
