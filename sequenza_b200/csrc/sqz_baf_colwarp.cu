@@ -533,12 +533,11 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
 #define SQZ_CW(PTV, NCV, SBV, OCCV)                                                       \
   rc = launch_colwarp<PTV, NCV, SBV, OCCV>(a, m, N_total, cwg, (int)ic0, nCb, (int)ua,    \
                                            (int)(ub - ua), partM, partE, stats, st)
-    const char* var_env = getenv("SQZ_CW_VARIANT");  // experiments only
-    const int variant = var_env ? atoi(var_env) : 0;
+    // (measured and dropped: two segments per stage, 36.4 ms against 34.4; twelve warps
+    // per SM at 168 registers with two per stage, 51 ms -- the spills cost more than the
+    // occupancy gains)
     if (m.nc == 8) {
       if (PT == 16) SQZ_CW(16, 8, cw_batch(8), 8);
-      else if (variant == 1) SQZ_CW(32, 8, 2, 12);
-      else if (variant == 2) SQZ_CW(32, 8, 2, 8);
       else SQZ_CW(32, 8, cw_batch(8), 8);
     } else {
       if (PT == 16) SQZ_CW(16, 21, cw_batch(21), 8);

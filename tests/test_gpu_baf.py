@@ -138,6 +138,29 @@ def test_baf_bayes_degenerate_rows(oracle):
         assert rel_close(a[:, 3], b[:, 3])
 
 
+def test_baf_model_view_lattice(oracle):
+    """The baf.bayes call of baf.model.view (R/graphics.R:410-425): a 100 x 50 lattice
+    expand.grid(Bf = seq(0.001, 0.5, 0.005), ratio = seq(0.01, 2.5, 0.05)), Bf fastest,
+    scalar sd (the mean segment sd) and weights 10 / 10, at the fitted solution, with the
+    CNt.max of sequenza.fit (7) and of sequenza.results (20, R/results.R:226)."""
+    bf, ratio = S.r_seq(0.001, 0.5, 0.005), S.r_seq(0.01, 2.5, 0.05)
+    assert bf.size == 100 and ratio.size == 50
+    Bf = np.tile(bf, ratio.size)          # expand.grid: first factor varies fastest
+    dr = np.repeat(ratio, bf.size)
+    for cn_max in (7, 20):
+        kw = dict(cellularity=0.88, ploidy=2.0, avg_depth_ratio=1.0, sd_Bf=0.0731,
+                  weight_Bf=10, sd_ratio=0.6124, weight_ratio=10, CNt_max=cn_max, CNt_min=0,
+                  CNn=2, ratio_priority=False)
+        got = S.baf_bayes(Bf, dr, **kw)
+        ref, margin = oracle.baf_bayes(Bf, dr, return_margin=True, **kw)
+        tie = (margin > 0) & (margin < 1e-12)
+        for col in range(3):
+            assert np.all((got[:, col] == ref[:, col]) | tie), col
+        assert rel_close(got[:, 3], ref[:, 3])
+        z = got[:, 3].reshape(ratio.size, bf.size).T  # tapply(LPP, list(Bf, ratio), mean)
+        assert z.shape == (100, 50) and np.isfinite(z).all()
+
+
 def test_baf_bayes_empty():
     out = S.baf_bayes([], [], 0.5, 2.0, 1.0)
     assert out.shape == (0, 4)
