@@ -315,7 +315,8 @@ def measure_grid(w, env, steps, warmup, with_e2e=True):
     evals_total = float(nC) * nP * n
 
     dev = BafGridDevice(device=device, **w["args"])
-    fit = DistributedGridFit(dev, pl, ce, peer=True, CNt_max=w["cn_max"], priors_table=PRI)
+    fit = DistributedGridFit(dev, pl, ce, peer=os.environ.get("SQZ_NO_PEER", "") != "1",
+                             CNt_max=w["cn_max"], priors_table=PRI)
     plan = fit.plan
     flush = env["flush"]
 
