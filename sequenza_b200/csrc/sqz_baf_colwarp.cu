@@ -18,7 +18,7 @@
 //             nothing is shared between them and the hardware scheduler balances them;
 //             the tiles of one (group, chunk) are neighbours in the grid and find each
 //             other's rows in L2.
-//   ring      two stages of cw_batch() segments; lane 0 fills a stage with one TMA bulk copy
+//   ring      two stages of 4 (CNt 0..7) or 1-2 (CNt 0..20) segments; lane 0 fills a stage with one TMA bulk copy
 //             (plus one for the segments' ratio terms) and completion is counted on an
 //             mbarrier; the stage is refilled as soon as the warp has left it.
 //   batch     the segments of a stage are analysed together (bounds, argmin, dynamic loads,
@@ -50,7 +50,7 @@ namespace sqz {
 namespace {
 // Segments per stage of the ring = segments whose analyses run together (their serial
 // chains overlap in one basic block).  Two stages: one is worked on, the other in flight.
-__host__ __device__ constexpr int cw_batch(int nc) { return nc <= 8 ? 4 : 1; }
+// (4 for CNt 0..7; 1 or 2 for CNt 0..20, see baf_colwarp_run)
 constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 }  // namespace
 
@@ -508,8 +508,8 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
                     cudaStream_t st, unsigned long long* stats) {
   if (!baf_colwarp_supported(m.nc, m.CNt_min, m.T, a.rp != 0))
     return fail(SQZ_ERR_ARG, "column-per-lane kernel: unsupported model");
-  if (PT != 16 && PT != 32)
-    return fail(SQZ_ERR_ARG, "column-per-lane kernel: ploidy tile must be 16 or 32");
+  if (PT != 8 && PT != 16 && PT != 32)
+    return fail(SQZ_ERR_ARG, "column-per-lane kernel: ploidy tile must be 8, 16 or 32");
   int64_t groups = (int64_t)(cw_bytes / baf_colwarp_group_bytes(m.nc, N_total));
   if (groups < 1) return fail(SQZ_ERR_SIZE, "column-per-lane kernel needs room for 32 columns");
   if (groups > 2047) groups = 2047;
@@ -537,11 +537,15 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
     // per SM at 168 registers with two per stage, 51 ms -- the spills cost more than the
     // occupancy gains)
     if (m.nc == 8) {
-      if (PT == 16) SQZ_CW(16, 8, cw_batch(8), 8);
-      else SQZ_CW(32, 8, cw_batch(8), 8);
+      if (PT == 8) SQZ_CW(8, 8, 4, 8);
+      else if (PT == 16) SQZ_CW(16, 8, 4, 8);
+      else SQZ_CW(32, 8, 4, 8);
     } else {
-      if (PT == 16) SQZ_CW(16, 21, cw_batch(21), 8);
-      else SQZ_CW(32, 21, cw_batch(21), 8);
+      // 21 copy numbers: a stage is 5.25 KB per segment; narrow tiles leave room (registers
+      // and shared memory) for two segments per stage
+      if (PT == 8) SQZ_CW(8, 21, 2, 8);
+      else if (PT == 16) SQZ_CW(16, 21, 1, 8);
+      else SQZ_CW(32, 21, 1, 8);
     }
 #undef SQZ_CW
     if (rc) return rc;

@@ -677,7 +677,7 @@ static int colwarp_tile(const CnModel& m, bool rp, int64_t N_total, int64_t S, i
   const int e = env_int("SQZ_COLWARP", -1);  // 0/1 override (experiments and tests only)
   if (e == 0 || !baf_colwarp_supported(m.nc, m.CNt_min, m.T, rp) || N_total <= 0) return 0;
   const int pt_env = env_int("SQZ_PT", 0);
-  if (e == 1) return (pt_env == 16 || pt_env == 32) ? pt_env : (nP <= 96 ? 16 : 32);
+  if (e == 1) return (pt_env == 8 || pt_env == 16 || pt_env == 32) ? pt_env : (nP <= 96 ? 16 : 32);
   const int64_t groups = (nC + 31) / 32;
   if (nC * 10 < groups * 32 * 6) return 0;
   const int64_t slots = 148 * 8, ch = colwarp_chunks(N_total, S);
