@@ -541,9 +541,10 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
       else if (PT == 16) SQZ_CW(16, 8, 4, 8);
       else SQZ_CW(32, 8, 4, 8);
     } else {
-      // 21 copy numbers: a stage is 5.25 KB per segment; narrow tiles leave room (registers
-      // and shared memory) for two segments per stage
-      if (PT == 8) SQZ_CW(8, 21, 2, 8);
+      // 21 copy numbers: a stage is 5.25 KB per segment, one segment per stage; the narrow
+      // tile needs 158 registers, so twelve warps fit an SM (measured: two segments per
+      // stage and seven warps, 1.24-1.27 ms on config 2 against 1.08)
+      if (PT == 8) SQZ_CW(8, 21, 1, 12);
       else if (PT == 16) SQZ_CW(16, 21, 1, 8);
       else SQZ_CW(32, 21, 1, 8);
     }

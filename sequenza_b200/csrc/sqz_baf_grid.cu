@@ -656,6 +656,23 @@ static int64_t colwarp_chunks(int64_t N_total, int64_t S) {
   return k < 1 ? 1 : k;
 }
 
+constexpr int64_t kNarrowMaxChunks = 128;
+// Chunk count of the column-per-lane kernel with 8-wide tiles (twelve one-warp CTAs per SM):
+// the units of the WHOLE grid times the chunks should fill the machine in whole waves.
+static int64_t narrow_chunks(int64_t N_total, int64_t S, int64_t units_total) {
+  const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+  int64_t cap = avg / 128;
+  if (cap > kNarrowMaxChunks) cap = kNarrowMaxChunks;
+  if (S > 1 && cap > 2048 / S) cap = 2048 / S;
+  if (cap < 1) cap = 1;
+  const int64_t slots = 148 * 12, ctas = (units_total > 0 ? units_total : 1) * (S > 0 ? S : 1);
+  int64_t best = slots / ctas;  // one wave
+  for (int64_t k = 2; k <= 4; ++k)
+    if (k * slots / ctas <= cap) best = k * slots / ctas;
+  if (best > cap) best = cap;
+  return best < 1 ? 1 : best;
+}
+
 // Largest chunk count either planner may pick; the partial buffers are sized for it.
 // Segment-per-lane kernels keep >= 8 segments per thread of a 64-thread CTA.
 static int64_t max_chunks(int64_t N_total, int64_t S) {
@@ -664,6 +681,14 @@ static int64_t max_chunks(int64_t N_total, int64_t S) {
   if (a > 64) a = 64;
   const int64_t b = colwarp_chunks(N_total, S);
   if (b > a) a = b;
+  // the narrow-tile column-per-lane plan (CNt 0..20 on a coarse ploidy axis) fills the
+  // machine with chunks of 128 segments or more, at most kNarrowMaxChunks of them
+  int64_t c = avg / 128;
+  if (c > kNarrowMaxChunks) c = kNarrowMaxChunks;
+  if (S > 1 && c > 2048 / S) c = 2048 / S;
+  if (c > a) a = c;
+  const int64_t e = env_int("SQZ_CW_MAXCHUNKS", 0);  // experiments: room for SQZ_CHUNKS
+  if (e > a && e <= 512 && S == 1 && avg / e >= 32) a = e;
   return a < 1 ? 1 : a;
 }
 
@@ -682,9 +707,16 @@ static int colwarp_tile(const CnModel& m, bool rp, int64_t N_total, int64_t S, i
   if (nC * 10 < groups * 32 * 6) return 0;
   const int64_t slots = 148 * 8, ch = colwarp_chunks(N_total, S);
   const int64_t u32 = S * groups * ((nP + 31) / 32) * ch, u16 = S * groups * ((nP + 15) / 16) * ch;
-  if (m.nc > 8)  // CNt 0..20: a coarse ploidy axis keeps 4-6 copy numbers alive per warp and
-                 // the plain split kernel is as fast (91 x 61 grid: 1.44 vs 1.50 ms)
-    return (nP >= 200 && u16 >= 2 * slots) ? 16 : 0;
+  if (m.nc > 8) {
+    // CNt 0..20.  Fine ploidy axes: 16-wide tiles.  Coarse ones (the default 91 x 61 grid):
+    // 8-wide tiles keep about three copy numbers alive per warp, and with one segment per
+    // stage twelve warps fit an SM -- 1.08 ms against the split kernel's 1.40 on config 2
+    // (1.30 / 1.40 with every sd x 0.1, where most candidates survive); short tables stay
+    // with the split kernel.
+    if (nP >= 200 && u16 >= 2 * slots) return 16;
+    const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
+    return (avg >= 4096 && nP >= 16) ? 8 : 0;
+  }
   // 32-wide tiles need fewer instructions per evaluation; 16-wide ones give twice the units
   // and a cheaper per-chunk prologue.  Measured (tools/colwarp_vs_pruned.py,
   // tools/shard_tile_width.py): 32 wins from 6 waves of units on, and from 2 waves on when
@@ -706,7 +738,9 @@ static GridPlan plan_fit(int64_t N_total, int64_t S, int64_t nP, int64_t nC, con
     g.PT = cw_pt;
     g.nPT = (int)((nP + g.PT - 1) / g.PT);
     g.threads = 32;  // one warp per CTA
-    g.nChunk = (int)colwarp_chunks(N_total, S);
+    g.nChunk = (int)(g.PT == 8 && m.nc > 8
+                         ? narrow_chunks(N_total, S, ((nC + 31) / 32) * g.nPT)
+                         : colwarp_chunks(N_total, S));
     const int ch_env = env_int("SQZ_CHUNKS", 0);
     if (ch_env >= 1 && ch_env <= max_chunks(N_total, S)) g.nChunk = ch_env;
     return g;

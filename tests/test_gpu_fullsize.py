@@ -81,16 +81,26 @@ def windows_around(k, nP, G, width=32, extra=()):
 
 def test_config2_full_size_vs_oracle(oracle):
     """BASELINE configs[1] exactly as bench.py runs it: 3e4 segments, CNt.max = 20, default
-    91 x 61 grid -> split kernel.  128 oracle grid points at full N."""
+    91 x 61 grid -> column-per-lane kernel with 8-wide tiles.  128 oracle grid points at
+    full N; the split kernel (forced) is held to the same windows."""
     seg = synth_segments(30000, seed=DEFAULT_SEED)
     ce, pl = S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1)
     kw = dict(cellularity=ce, ploidy=pl, CNt_max=20, priors_table=PRI, **baf_args(seg))
     got, path = grid_with_path(lambda: S.baf_grid_sums(**kw))
-    assert path == 1, "config 2 is expected on the split kernel, got path %d" % path
+    assert path == 3, "config 2 is expected on the column-per-lane kernel, got path %d" % path
     k, margin = top2_margin(got)
     nP, G = pl.size, got.size
     wins = windows_around(k, nP, G, extra=(0, 45 * nP + 10, G - 32))  # incl. cellularity = 1
-    worst = check_windows(got, oracle_windows(oracle, wins, **kw))
+    refs = oracle_windows(oracle, wins, **kw)
+    worst = check_windows(got, refs)
+    os.environ["SQZ_COLWARP"] = "0"
+    try:
+        split, path = grid_with_path(lambda: S.baf_grid_sums(**kw))
+    finally:
+        del os.environ["SQZ_COLWARP"]
+    assert path == 1
+    check_windows(split, refs)
+    assert int(np.argmax(split)) == k
     ref = oracle.baf_grid_sums(g0=wins[0][0], g1=wins[0][1], nthreads=CORES, **kw)
     assert wins[0][0] + int(np.argmax(ref)) == k  # the selected solution, bit-exact
     assert margin > 10 * RTOL, "top-2 margin %.3g too small for the tolerance to decide" % margin

@@ -22,12 +22,18 @@ def no_overrides(monkeypatch):
         monkeypatch.delenv(k, raising=False)
 
 
-def test_config2_takes_the_split_kernel():
-    # 91 x 61 grid, CNt 0..20: a coarse ploidy axis, 128-thread CTAs, 32-wide tiles
+def test_config2_takes_narrow_column_per_lane_tiles():
+    # 91 x 61 grid, CNt 0..20, 3e4 segments: 8-wide tiles, 3 column groups x 8 tiles = 24
+    # units, and 74 chunks so that 24 x 74 one-warp CTAs are one wave of 148 SMs x 12
     p = plan(30000, 1, 61, 91, 20)
-    assert (p["PT"], p["nPT"], p["threads"], p["T"]) == (32, 2, 128, 121)
-    assert FAMILY[p["family"]] == "split" and p["W"] == 1 and p["units"] == 91 * 2
-    assert 1 <= p["chunks"] <= 64
+    assert (p["PT"], p["nPT"], p["threads"], p["T"]) == (8, 8, 32, 121)
+    assert FAMILY[p["family"]] == "colwarp" and p["W"] == 32 and p["units"] == 24
+    assert p["chunks"] == 74
+    # a short table, ratio.priority or an unsorted ploidy axis: the split kernel
+    q = plan(3000, 1, 61, 91, 20)
+    assert (q["PT"], q["nPT"], q["threads"]) == (32, 2, 128) and FAMILY[q["family"]] == "split"
+    assert q["W"] == 1 and q["units"] == 91 * 2 and 1 <= q["chunks"] <= 64
+    assert FAMILY[plan(30000, 1, 61, 91, 20, rp=1)["family"]] == "split"
 
 
 def test_config3_takes_the_column_per_lane_kernel():
@@ -85,8 +91,9 @@ def test_workspace_sizes():
     assert L.sqz_baf_grid_workspace_bytes(300000, 1, 61, 91) > base
     assert L.sqz_baf_grid_workspace_bytes(0, 0, 0, 0) > 0
     # preferred = minimum + scratch: 8 B x 21 x N per column for the split kernel ...
-    pref = L.sqz_baf_grid_workspace_preferred_bytes(30000, 1, 61, 91, 91, 21, 0)
-    assert pref - base == pytest.approx(91 * 21 * 30000 * 8, rel=1e-6)
+    b2 = L.sqz_baf_grid_workspace_bytes(3000, 1, 61, 91)
+    pref = L.sqz_baf_grid_workspace_preferred_bytes(3000, 1, 61, 91, 91, 21, 0)
+    assert pref - b2 == pytest.approx(91 * 21 * 3000 * 8, abs=512)
     # ... 8 B x 8 x N per column in whole 32-column groups for the column-per-lane kernel
     b3 = L.sqz_baf_grid_workspace_bytes(100000, 1, 601, 901)
     p3 = L.sqz_baf_grid_workspace_preferred_bytes(100000, 1, 601, 901, 901, 8, 0)
