@@ -13,7 +13,7 @@ Workloads
       CNt.max = 7, grid 901 x 601, cut into units of 32 columns x 32 ploidies that are
       dealt to the N GPUs (strong scaling: total work fixed).  At N = 1 the line also
       carries `extra.config2` (BASELINE configs[1]: 3e4 segments, CNt.max = 20, 91 x 61,
-      the single-GPU configuration) and `extra.worst_case` (config 3 with every sd x 10,
+      the single-GPU configuration) and `extra.worst_case` (config 3 with every sd x 0.1,
       where candidate pruning helps least).
   config2: BASELINE configs[1] as the headline (one GPU).
   config4: mufreq.bayes on 1e7 SNV positions (BASELINE configs[3]); metric positions/s.
@@ -73,9 +73,10 @@ def make_workload(name: str):
         raise SystemExit("unknown grid workload %s" % name)
     seg = synth_segments(n, cn_max=7, seed=DEFAULT_SEED)
     if name == "worst_case":
-        seg["sd_ratio"] = seg["sd_ratio"] * 10.0
-        seg["sd_Bf"] = seg["sd_Bf"] * 10.0
-        desc = "config 3 with sd.ratio and sd.BAF x 10 (flat likelihood: least pruning)"
+        seg["sd_ratio"] = seg["sd_ratio"] * 0.1
+        seg["sd_Bf"] = seg["sd_Bf"] * 0.1
+        desc = ("config 3 with sd.ratio and sd.BAF x 0.1 (sharp likelihood: the candidate "
+                "pruning keeps the most copy numbers; x 10 is faster than x 1)")
     return {"name": name, "args": baf_args(seg), "ce": ce, "pl": pl, "cn_max": cn_max,
             "n": n, "scaling": "strong", "desc": desc,
             "n_c": cn_max + 1, "T": sum(c // 2 + 1 for c in range(cn_max + 1))}

@@ -1,0 +1,14 @@
+#!/bin/bash
+# 8-GPU job: multi-GPU tests, strong scaling of config 3 at N = 8 and 4, chunk-count variant.
+mkdir -p gpurun_out
+run() { # N tag [env...]
+  n=$1; tag=$2; shift 2
+  env "$@" timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29700 + RANDOM % 200)) bench.py --gpus $n --steps 20 --warmup 5 > gpurun_out/j8_$tag.json 2> gpurun_out/j8_$tag.err
+  echo "$tag rc=$?"; python tools/brief.py < gpurun_out/j8_$tag.json
+}
+timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -x -q > gpurun_out/j8_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/j8_pytest.log; tail -2 gpurun_out/j8_pytest.log
+run 8 n8 A=1
+run 8 n8_c128 SQZ_CW_MAXCHUNKS=128
+run 8 n8_nccl SQZ_NO_PEER=1
+run 4 n4 A=1
+timeout 300 python bench.py --steps 10 --warmup 3 --workload config5 --gpus 8 > gpurun_out/j8_config5.json 2> gpurun_out/j8_config5.err; head -c 400 gpurun_out/j8_config5.json
