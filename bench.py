@@ -354,11 +354,21 @@ def measure_grid(w, env, steps, warmup, with_e2e=True):
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     ms_per_step = float(tm.item()) / steps
     lpp_sum = res[0].cpu().numpy().copy()
+    # this rank's own phases, and everybody's (the step ends when the slowest rank is done)
+    mine = torch.tensor([ms3[0], ms3[1], ms3[2], step_ms], dtype=torch.float64,
+                        device=device) / max(ncall.value, 1)
+    if world > 1:
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+    else:
+        allr = [mine]
+    per_rank = {k: [round(float(t[i]), 4) for t in allr]
+                for i, k in enumerate(("prep_ms", "grid_kernels_ms", "finalize_ms", "step_ms"))}
     out = {"plan": plan, "t0": t0, "t1": t1, "ms_per_step": ms_per_step,
            "value": evals_total / (ms_per_step * 1e-3), "lpp_sum": lpp_sum,
            "kpath": kpath.value, "n_cand": n_cand.value, "ncall": ncall.value,
            "ms3": [ms3[0], ms3[1], ms3[2]], "collective": fit.collective,
-           "units": (fit.u0, fit.u1),
+           "units": (fit.u0, fit.u1), "per_rank": per_rank,
            # kernels launched inside the timed region: the library's own count (preparation,
            # pre-pass, grid kernel, finalize, repair per fit) + the L2-flush fill + the two
            # kernels of the assembly (flag store + wait, or fill + NCCL all-reduce)
@@ -551,6 +561,7 @@ def run_ours(args, rank, world, local_rank):
                              "fits (sqz_profile_counters), plus per step the L2-flush fill "
                              "and, for N > 1, the two kernels of the assembly",
         "roofline": roofline_block(w, m, peak.value, world, local_rank),
+        "per_rank": m["per_rank"],
         "fit_wall_ms": m["e2e"]["ms_per_step"],
         "solution": {"cellularity": float(ce[k // nP]), "ploidy": float(pl[k % nP])},
     }
@@ -620,13 +631,14 @@ def run_other(args, env, local_rank):
     world, rank, device = env["world"], env["rank"], env["device"]
     if world > 1:
         dist.barrier(group=env["host_group"])
+    n_dev = max(world, args.gpus)  # plain `python bench.py --gpus N`: N devices, one process
     if rank == 0:
         sampler = ClockSampler(local_rank)
         sampler.start()
         t0 = time.perf_counter()
         stream = torch.cuda.current_stream().cuda_stream
         steps = max(3, args.steps)
-        base = {"n_gpus": world, "steps": steps, "warmup": max(args.warmup, 3),
+        base = {"n_gpus": n_dev, "steps": steps, "warmup": max(args.warmup, 3),
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic"}
         if args.workload == "config4":
@@ -705,7 +717,7 @@ def run_other(args, env, local_rank):
                 _lib.check(L.sqz_baf_grid_batch(
                     S_n, offs.ctypes.data, *[_lib.ptr(cat[k]) for k in keys], _lib.ptr(pl),
                     pl.size, _lib.ptr(ce), ce.size, _lib.ptr(adr), 0, 7, 2, _lib.ptr(pc),
-                    _lib.ptr(pv), 1, 0, world, 0, _lib.ptr(out)))
+                    _lib.ptr(pv), 1, 0, n_dev, 0, _lib.ptr(out)))
             for _ in range(3):
                 call()
             t = time.perf_counter()
@@ -728,10 +740,10 @@ def run_other(args, env, local_rank):
                                 "samples": S_n, "segments": S_n * n_seg, "grid": [91, 61]},
                         e2e={"value": evals / (ms * 1e-3), "unit": "evals/s", "ms_per_step": ms,
                              "h2d_bytes_per_step": 48 * S_n * n_seg, "d2h_bytes_per_step": 8 * S_n * G,
-                             "api": "sqz_baf_grid_batch(n_gpus=%d), pageable host vectors" % world},
+                             "api": "sqz_baf_grid_batch(n_gpus=%d), pageable host vectors" % n_dev},
                         value_note="timed through the host API (there is no resident-input "
                                    "form of the cohort call in this bench): value == e2e",
-                        gpu_launches=5 * steps * world,
+                        gpu_launches=5 * steps * n_dev,
                         cpu_baseline={"value": ref.size * n_seg / tc, "unit": "evals/s",
                                       "cores": os.cpu_count() or 1, "kind": "port",
                                       "sample": "%d grid points of one sample, %.1f s" % (ref.size, tc)})
@@ -743,10 +755,10 @@ def run_other(args, env, local_rank):
             ce, pl = S.r_seq(0.1, 1, 0.01), S.r_seq(1, 7, 0.1)
             kw = dict(mufreq=mut["mufreq"], depth_ratio=mut["depth_ratio"], cellularity=ce,
                       ploidy=pl, avg_depth_ratio=1.0, weight_mufreq=wv, weight_ratio=2 * wv)
-            S.mufreq_grid_sums(n_gpus=world, **kw)
+            S.mufreq_grid_sums(n_gpus=n_dev, **kw)
             t = time.perf_counter()
             for _ in range(steps):
-                got = S.mufreq_grid_sums(n_gpus=world, **kw)
+                got = S.mufreq_grid_sums(n_gpus=n_dev, **kw)
             ms = (time.perf_counter() - t) * 1e3 / steps
             cores = os.cpu_count() or 1
             tc = time.perf_counter()
@@ -765,7 +777,7 @@ def run_other(args, env, local_rank):
                              "h2d_bytes_per_step": 32 * n, "d2h_bytes_per_step": 8 * 5551,
                              "api": "sqz_mufreq_grid (host pointers)"},
                         value_note="timed through the host API: value == e2e",
-                        gpu_launches=2 * steps * world,
+                        gpu_launches=2 * steps * n_dev,
                         cpu_baseline={"value": ref.size * n / tc, "unit": "evals/s",
                                       "cores": cores, "kind": "port",
                                       "sample": "%d grid points x 1e4 positions, %.1f s" % (ref.size, tc)})

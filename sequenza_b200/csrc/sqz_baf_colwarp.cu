@@ -160,17 +160,23 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const double adr = a.adr[smp];
 
   // ---- per-thread model: nld_j = -log D_j centred on the tile midpoint -----------------
+  // (the logarithms run in rolled loops through the not yet used stage buffer: one copy of
+  // log() in the kernel instead of PT + NC inlined ones keeps the code small enough for the
+  // instruction cache when every warp of an SM is at a different place)
   double nld[PT];
-#pragma unroll
+  static_assert(PT * 32 <= kRing * kSegB * kSegDoubles, "stage buffer too small for the set-up");
+#pragma unroll 1
   for (int j = 0; j < PT; ++j) {
     const int ip = min(p0 + j, a.nP - 1);  // ragged last tile repeats the last ploidy
-    nld[j] = -log((a.ploidy[ip] / 2.0 * cell) + 1 - cell);
+    stage[j * 32 + lane] = -log((a.ploidy[ip] / 2.0 * cell) + 1 - cell);
   }
+#pragma unroll
+  for (int j = 0; j < PT; ++j) nld[j] = stage[j * 32 + lane];
   const double nmid = 0.5 * (nld[0] + nld[PT - 1]);
 #pragma unroll
   for (int j = 0; j < PT; ++j) nld[j] -= nmid;
   const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
-#pragma unroll
+#pragma unroll 1
   for (int c = 0; c < NC; ++c) {
     const double A = (1 - cell) + ((double)(m.CNt_min + c) / (double)m.CNn * cell);
     lm[c * 32] = log(adr * A) + nmid;
@@ -447,10 +453,15 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   if (icl_raw >= nCb) return;
   const int64_t Gs = (int64_t)a.nCs * a.nP;
   const int64_t o = ((int64_t)chunk * a.S + smp) * Gs + (int64_t)(ic0 + icl) * a.nP + p0;
+  // the products leave through the (drained) stage buffer so that the loop with the
+  // logarithm can stay rolled; a lane reads back only its own values
 #pragma unroll
+  for (int j = 0; j < PT; ++j) stage[j * 32 + lane] = P[j];
+#pragma unroll 1
   for (int j = 0; j < PT; ++j) {
     if (p0 + j < a.nP) {
-      const int hi = __double2hiint(P[j]), lo = __double2loint(P[j]);
+      const double pj = stage[j * 32 + lane];
+      const int hi = __double2hiint(pj), lo = __double2loint(pj);
       const bool bd = ((bad >> j) & 1u) || (unsigned)(hi - 0x00100000) >= 0x7FE00000u;
       const double v = log(__hiloint2double((hi & 0x000FFFFF) | 0x3FF00000, lo));
       partM[o + j] = bd ? __longlong_as_double(0x7FF8000000000000LL) : v;
