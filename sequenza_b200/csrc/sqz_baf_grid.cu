@@ -639,20 +639,22 @@ static int prune_mode(int nc, bool monotone, bool rp) {
 
 // Chunk count of the column-per-lane kernel.  It follows the segment table only.  Every
 // warp of that kernel walks all segments of its chunk: at least 64 per chunk, at most 64
-// chunks, fewer for a cohort (the samples already fill the machine, and
+// chunks (128 for one long table), fewer for a cohort (the samples already fill the machine, and
 // every chunk costs a slab of partial results).
-constexpr int64_t kColwarpMaxChunks = 64;
+constexpr int64_t kColwarpMaxChunks = 128;
 static int64_t colwarp_chunks(int64_t N_total, int64_t S) {
   const int64_t avg = S > 0 ? (N_total + S - 1) / S : 0;
-  int64_t top = S > 0 ? 2048 / S : kColwarpMaxChunks;
-  if (top > kColwarpMaxChunks) top = kColwarpMaxChunks;
+  int64_t top = S > 0 ? 2048 / S : 64;
+  if (top > 64) top = 64;
   int64_t k = avg / 64;
   if (k > top) k = top;
-  // Experiments only: more, shorter chunks for one long table.  Measured on config 3 (1e5
-  // segments): 128 chunks of 781 segments cost 5 % on one GPU (34.4 vs 32.7 ms) and the
-  // idle tail of an eighth of the grid is the same (3.7 vs 7.5 waves of one-warp CTAs).
+  // One long table: up to 128 chunks of 512 segments or more.  An eighth of the fine grid
+  // (one GPU of eight) is then 7.5 waves of one-warp CTAs instead of 3.7, and the idle tail
+  // at the end of the kernel shrinks with the CTAs: measured on config 3, 64 -> 128 chunks
+  // costs 1.8 % on one GPU (32.9 -> 33.5 ms) and gains 4.4 % on the slowest of eight
+  // shards (4.96 -> 4.74 ms).  (SQZ_CW_MAXCHUNKS: experiments only.)
   const int64_t cap = env_int("SQZ_CW_MAXCHUNKS", (int)kColwarpMaxChunks);
-  if (cap > kColwarpMaxChunks && S == 1 && avg / 512 > 64) k = avg / 512 < cap ? avg / 512 : cap;
+  if (S == 1 && avg / 512 > 64) k = avg / 512 < cap ? avg / 512 : cap;
   return k < 1 ? 1 : k;
 }
 

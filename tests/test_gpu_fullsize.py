@@ -109,7 +109,7 @@ def test_config2_full_size_vs_oracle(oracle):
 
 def test_config3_full_size_vs_oracle(oracle):
     """BASELINE configs[2]: 1e5 segments, CNt.max = 7, the whole 901 x 601 grid -> the
-    column-per-lane kernel with 32-wide tiles and 64 segment chunks.  160 oracle grid
+    column-per-lane kernel with 32-wide tiles and 128 segment chunks.  160 oracle grid
     points at full N, the window around the selected solution among them."""
     import torch
     from sequenza_b200.dist import BafGridDevice, grid_plan, shard_columns, shard_units

@@ -41,7 +41,7 @@ def test_config3_takes_the_column_per_lane_kernel():
     p = plan(100000, 1, 601, 901, 7)
     assert (p["PT"], p["nPT"], p["threads"], p["T"]) == (32, 19, 32, 20)
     assert FAMILY[p["family"]] == "colwarp" and p["W"] == 32 and p["units"] == 29 * 19
-    assert p["chunks"] == 64
+    assert p["chunks"] == 128
     # the same grid over 3,000 segments (46 per chunk) takes 16-wide tiles
     q = plan(3000, 1, 601, 181, 7)
     assert (q["PT"], q["threads"]) == (16, 32)
