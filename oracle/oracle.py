@@ -24,8 +24,9 @@ NA_REAL_BITS = 0x7FF00000000007A2
 
 def build(force: bool = False) -> str:
     """Compile the oracle with the committed Makefile (gcc, no R needed)."""
-    src = os.path.join(_HERE, "sqz_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("sqz_oracle.c", "sqz_oracle_segstats.c")]
+    if force or not os.path.exists(_SO) or \
+            os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "libsqz_oracle.so"])
     return _SO
 
@@ -70,6 +71,10 @@ def lib():
         _lib.sqzo_normalise_lpp.restype = None
         _lib.sqzo_normalise_lpp.argtypes = [i64, p, p]
         _lib.sqzo_max_threads.restype = i
+        _lib.sqzo_b_allele_freq_mode.restype = d
+        _lib.sqzo_b_allele_freq_mode.argtypes = [p, p, p, i64, p]
+        _lib.sqzo_segment_stats.restype = i
+        _lib.sqzo_segment_stats.argtypes = [i64, p, p] + [p] * 8 + [d, i, p]
     return _lib
 
 
@@ -309,3 +314,35 @@ def get_ci(cp_table, level=0.95):
         "confint.cellularity": (min(cy), max(cy)),
         "max.cellularity": cell[first_max(vy)],
     }
+
+
+# ---- R/segments.R, R/model.R:69-98 -----------------------------------------------
+def b_allele_freq_mode(Af, Bf, good_reads, return_density=False):
+    """b_allele_freq(Af, Bf, good.reads)[2] (R/model.R:69-98): the mode of the weighted
+    kernel density of c(Bf, Af), folded to <= 0.5."""
+    a, b, g = _vec(Af), _vec(Bf), _vec(good_reads)
+    dens = np.empty(512)
+    v = lib().sqzo_b_allele_freq_mode(_ptr(a), _ptr(b), _ptr(g), b.size, _ptr(dens))
+    return (v, dens) if return_density else v
+
+
+SEGMENT_COLUMNS = ("Bf", "N.BAF", "sd.BAF", "depth.ratio", "N.ratio", "sd.ratio")
+
+
+def segment_stats(row_off, seg_off, position, adjusted_ratio, depth_normal, good_reads, Af,
+                  Bf, is_het, breaks_vect, min_reads_baf=1, weighted_mean=True):
+    """The per-segment statistics of segment.breaks (R/segments.R:113-198) for a genome laid
+    out as concatenated chromosomes; returns an n_seg x 6 array, columns SEGMENT_COLUMNS."""
+    ro = np.ascontiguousarray(row_off, dtype=np.int64)
+    so = np.ascontiguousarray(seg_off, dtype=np.int64)
+    cols = [_vec(v) for v in (position, adjusted_ratio, depth_normal, good_reads, Af, Bf)]
+    het = np.ascontiguousarray(is_het, dtype=np.uint8)
+    brk = _vec(breaks_vect)
+    S = int(so[-1])
+    out = np.empty((6, S))
+    rc = lib().sqzo_segment_stats(ro.size - 1, _ptr(ro), _ptr(so), *[_ptr(c) for c in cols],
+                                  _ptr(het), _ptr(brk), float(min_reads_baf),
+                                  int(bool(weighted_mean)), _ptr(out))
+    if rc:
+        raise MemoryError("oracle segment_stats")
+    return out.T.copy()
