@@ -20,6 +20,8 @@ Workloads
   config5: cohort of 512 samples in one call (BASELINE configs[4]), sqz_baf_grid_batch
       with n_gpus = N from one process.
   mufreq_grid: mufreq.model.fit (R/bayes.R:175-194) on 1e4 positions x 91 x 61.
+  segstats: segment.breaks' per-segment statistics (R/segments.R:113-198) over a synthetic
+      genome of 2.4e7 seqz rows, 24 chromosomes, 2,400 segments; metric rows/s.
 
 Arms
   ours       value: inputs resident in HBM, CUDA events on the launch stream, max over
@@ -527,7 +529,7 @@ def run_ours(args, rank, world, local_rank):
            "flush": torch.empty(256 << 20, dtype=torch.uint8, device=device)}  # > 126 MB L2
     if world > 1:
         env["host_group"] = dist.new_group(backend="gloo")
-    if args.workload in ("config4", "config5", "mufreq_grid"):
+    if args.workload in ("config4", "config5", "mufreq_grid", "segstats"):
         return run_other(args, env, local_rank)
     w = make_workload(args.workload)
     sampler = ClockSampler(local_rank)
@@ -747,6 +749,66 @@ def run_other(args, env, local_rank):
                         cpu_baseline={"value": ref.size * n_seg / tc, "unit": "evals/s",
                                       "cores": os.cpu_count() or 1, "kind": "port",
                                       "sample": "%d grid points of one sample, %.1f s" % (ref.size, tc)})
+        elif args.workload == "segstats":
+            from oracle import oracle as O
+            from sequenza_b200 import segments as G
+            g = G.synth_seqz(n_chr=24, rows_per_chr=1_000_000, segs_per_chr=100, seed=11)
+            n_rows, n_seg = int(g["row_off"][-1]), int(g["seg_off"][-1])
+            keys = ("position", "adjusted_ratio", "depth_normal", "good_reads", "Af", "Bf")
+            dv = [torch.from_numpy(g[k]).to(device) for k in keys]
+            dhet = torch.from_numpy(g["is_het"]).to(device)
+            dro = torch.from_numpy(g["row_off"]).to(device)
+            dso = torch.from_numpy(g["seg_off"]).to(device)
+            dbrk = torch.from_numpy(g["breaks_vect"]).to(device)
+            wsb = L.sqz_segment_stats_workspace_bytes(n_seg)
+            ws = torch.empty(wsb + 256, dtype=torch.uint8, device=device)
+            wsp = (ws.data_ptr() + 255) & ~255
+            dout = torch.empty(6 * n_seg, dtype=torch.float64, device=device)
+
+            def call():
+                _lib.check(L.sqz_segment_stats_dev(
+                    24, dro.data_ptr(), dso.data_ptr(), n_seg, *[t.data_ptr() for t in dv],
+                    dhet.data_ptr(), dbrk.data_ptr(), 1.0, 1, wsp, wsb, stream, dout.data_ptr()))
+            ms = timed_ms(torch, call, steps, args.warmup, env["flush"])
+            got = dout.cpu().numpy().reshape(6, n_seg).T
+            te = time.perf_counter()
+            host = G.segment_stats(g["row_off"], g["seg_off"], *[g[k] for k in keys], g["is_het"],
+                                   g["breaks_vect"])
+            te = time.perf_counter() - te
+            assert np.array_equal(host, got, equal_nan=True)
+            c = 5  # CPU sample: one chromosome (1e6 rows, 100 segments)
+            r = slice(g["row_off"][c], g["row_off"][c + 1])
+            tc = time.perf_counter()
+            ref = O.segment_stats([0, 1_000_000], [0, 100], *[g[k][r] for k in keys],
+                                  g["is_het"][r], g["breaks_vect"][200 * c:200 * (c + 1)])
+            tc = time.perf_counter() - tc
+            mine = got[100 * c:100 * (c + 1)]
+            assert np.array_equal(mine[:, [1, 4]], ref[:, [1, 4]])
+            ok = ~np.isnan(ref)
+            assert np.max(np.abs(mine[ok] - ref[ok]) / np.maximum(np.abs(ref[ok]), 1e-300)) < 1e-12
+            peak, peak_src = hbm_peak()
+            # algorithmic bytes: every seqz column of every row once (6 x 8 + 1) + the table out
+            bytes_alg = 49.0 * n_rows + 48.0 * n_seg
+            line = dict(base, metric="seqz rows/sec, segment.breaks per-segment statistics (fp64)",
+                        value=n_rows / (ms * 1e-3), unit="rows/s", ms_per_step=ms,
+                        config={"workload": "segment.breaks statistics (R/segments.R:113-198, "
+                                "weighted.mean = TRUE) + b_allele_freq mode (R/model.R:69-98): "
+                                "2.4e7 synthetic seqz rows, 24 chromosomes, 2,400 segments, 30 % "
+                                "het", "rows": n_rows, "segments": n_seg,
+                                "l2": "256 MiB buffer written between timed iterations"},
+                        e2e={"value": n_rows / te, "unit": "rows/s", "ms_per_step": te * 1e3,
+                             "h2d_bytes_per_step": 49 * n_rows, "d2h_bytes_per_step": 48 * n_seg,
+                             "api": "sqz_segment_stats (pageable host vectors)"},
+                        gpu_launches=2 * steps,
+                        roofline={"bound": "hbm", "kernel": "segstat_reduce_kernel + "
+                                  "segstat_kde_kernel", "achieved": bytes_alg / (ms * 1e-3) / 1e9,
+                                  "peak": peak, "unit": "GB/s",
+                                  "frac": bytes_alg / (ms * 1e-3) / 1e9 / peak,
+                                  "peak_source": peak_src, "traffic": None,
+                                  "bytes_per_row": 49},
+                        cpu_baseline={"value": 1_000_000 / tc, "unit": "rows/s", "cores": 1,
+                                      "kind": "port", "sample": "one chromosome (1e6 rows, 100 "
+                                      "segments), oracle segment_stats, %.1f s" % tc})
         else:  # mufreq_grid
             from oracle import oracle as O
             n = 10000
@@ -794,7 +856,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="config3",
-                    choices=["config3", "config2", "config4", "config5", "mufreq_grid"])
+                    choices=["config3", "config2", "config4", "config5", "mufreq_grid",
+                             "segstats"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

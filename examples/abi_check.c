@@ -26,7 +26,9 @@ int main(void) {
       (fn_t)sqz_profile_counters, (fn_t)sqz_baf_grid_units_workspace_bytes,
       (fn_t)sqz_baf_grid_dev_units, (fn_t)sqz_peer_data_offset,
       (fn_t)sqz_peer_alloc, (fn_t)sqz_peer_open, (fn_t)sqz_peer_close,
-      (fn_t)sqz_peer_free, (fn_t)sqz_peer_signal, (fn_t)sqz_peer_wait};
+      (fn_t)sqz_peer_free, (fn_t)sqz_peer_signal, (fn_t)sqz_peer_wait,
+      (fn_t)sqz_segment_stats, (fn_t)sqz_segment_stats_workspace_bytes,
+      (fn_t)sqz_segment_stats_dev};
   printf("%s: %d entry points, %d device(s)\n", sqz_version(),
          (int)(sizeof syms / sizeof syms[0]), sqz_device_count());
   {

@@ -303,6 +303,44 @@ int sqz_fit_finish_dev(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t n
                        double* d_log_sum_lik, void* stream);
 
 /* ---------------------------------------------------------------------------------
+ * Before the grid: the per-segment statistics of segment.breaks, R/segments.R:113-198
+ * (weighted.mean = TRUE: :146-170, FALSE: :171-190), with b_allele_freq's kernel-density
+ * mode, R/model.R:69-98 -- the step that produces the segment table sequenza.fit filters
+ * and fits (R/extract.R:175-185 calls it per chromosome).  The breakpoints themselves
+ * (copynumber::aspcf, R/segments.R:1-111) stay with the caller.
+ *   rows       all chromosomes concatenated, chromosome c = rows row_off[c] ..
+ *              row_off[c+1]-1, sorted by position inside a chromosome; fp64 seqz columns
+ *              position, adjusted.ratio, depth.normal, good.reads, Af, Bf, and is_het (one
+ *              byte per row: zygosity.normal == "het").  NaN/NA_real_ are NA (na.rm = TRUE)
+ *   breaks     breaks_vect holds (start, end] of segment s at [2s], [2s+1]: the output of
+ *              unique.breaks (R/segments.R:133-139), increasing inside a chromosome;
+ *              chromosome c owns segments seg_off[c] .. seg_off[c+1]-1.  As cut() does, a
+ *              row belongs to a segment if start < position <= end
+ *   out        n_seg x 6 column-major: Bf, N.BAF, sd.BAF, depth.ratio, N.ratio, sd.ratio
+ *              (R/segments.R:164-170); NA where the reference has NA (sd of fewer than two
+ *              values, Bf without a het position)
+ * The final filter (N.ratio per Mb >= 2, R/segments.R:196-197) and the chromosome labels
+ * stay with the caller.  The density is density.default's algorithm (bw.nrd0, linear
+ * binning onto 512 points, gaussian kernel, approx) with the convolution summed directly
+ * instead of by FFT; one stated departure: a maximum whose top is a run of exactly equal
+ * values counts at its first point.
+ * The _dev form needs sqz_segment_stats_workspace_bytes(n_seg) bytes, 256-byte aligned.
+ * --------------------------------------------------------------------------------- */
+int sqz_segment_stats(int64_t n_chr, const int64_t* row_off, const int64_t* seg_off,
+                      const double* position, const double* adjusted_ratio,
+                      const double* depth_normal, const double* good_reads, const double* Af,
+                      const double* Bf, const unsigned char* is_het, const double* breaks_vect,
+                      double min_reads_baf, int weighted_mean, double* out);
+size_t sqz_segment_stats_workspace_bytes(int64_t n_seg);
+int sqz_segment_stats_dev(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
+                          int64_t n_seg, const double* d_position,
+                          const double* d_adjusted_ratio, const double* d_depth_normal,
+                          const double* d_good_reads, const double* d_Af, const double* d_Bf,
+                          const unsigned char* d_is_het, const double* d_breaks_vect,
+                          double min_reads_baf, int weighted_mean, void* workspace,
+                          size_t workspace_bytes, void* stream, double* d_out);
+
+/* ---------------------------------------------------------------------------------
  * Model points as the kernels compute them (R/model.R:49-67), for checking the device
  * arithmetic against tests/testthat/test.model.R.  out is T x 5 column-major:
  * CNt, second index (B or Mt), model depth.ratio, model BAF or mufreq, normalised prior.

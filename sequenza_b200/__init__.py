@@ -13,6 +13,7 @@ from .fit import sequenza_fit  # noqa: F401
 from .model import (baf_model_points, baf_types_matrix, device_model_points,  # noqa: F401
                     mufreq_model_points, mufreq_types_matrix, theoretical_baf,
                     theoretical_depth_ratio, theoretical_mufreq)
+from .segments import segment_breaks, segment_stats  # noqa: F401
 from .solutions import alternative_cp_solutions, get_ci  # noqa: F401
 
 __version__ = "0.1.0"

@@ -77,6 +77,13 @@ int fit_finish_launch(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t nC
                       double* d_znorm, double* d_row_max, double* d_col_max,
                       double* d_row_above, double* d_col_above, double* d_lsl,
                       cudaStream_t st);
+size_t segment_stats_workspace_bytes(int64_t n_seg);
+int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
+                         int64_t n_seg, const double* d_pos, const double* d_ratio,
+                         const double* d_dnorm, const double* d_good, const double* d_Af,
+                         const double* d_Bf, const unsigned char* d_het, const double* d_brk,
+                         double min_reads_baf, int weighted_mean, void* workspace,
+                         size_t workspace_bytes, cudaStream_t st, double* d_out);
 int model_points_launch(int kind, double cellularity, double ploidy, double adr, int CNt_min,
                         int CNt_max, int CNn, const double* prior_CN,
                         const double* prior_value, int n_prior, int* T_out, double* h_out);
@@ -837,6 +844,92 @@ int sqz_fit_finish(const double* lpp_sum, int64_t S, int64_t nP, int64_t nC, dou
   SQZ_CUDA(cudaMemcpyAsync(col_max, d_cm, nS * nC * 8, cudaMemcpyDeviceToHost, c->st));
   SQZ_CUDA(cudaMemcpyAsync(col_mass_above, d_ca, nS * nC * 8, cudaMemcpyDeviceToHost, c->st));
   SQZ_CUDA(cudaMemcpyAsync(log_sum_lik, d_l, nS * 8, cudaMemcpyDeviceToHost, c->st));
+  SQZ_CUDA(cudaStreamSynchronize(c->st));
+  return SQZ_OK;
+}
+
+size_t sqz_segment_stats_workspace_bytes(int64_t n_seg) {
+  return segment_stats_workspace_bytes(n_seg);
+}
+
+int sqz_segment_stats_dev(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
+                          int64_t n_seg, const double* d_position,
+                          const double* d_adjusted_ratio, const double* d_depth_normal,
+                          const double* d_good_reads, const double* d_Af, const double* d_Bf,
+                          const unsigned char* d_is_het, const double* d_breaks_vect,
+                          double min_reads_baf, int weighted_mean, void* workspace,
+                          size_t workspace_bytes, void* stream, double* d_out) {
+  if (sqz_device_count() < 1)
+    return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
+  return segment_stats_launch(n_chr, d_row_off, d_seg_off, n_seg, d_position, d_adjusted_ratio,
+                              d_depth_normal, d_good_reads, d_Af, d_Bf, d_is_het,
+                              d_breaks_vect, min_reads_baf, weighted_mean, workspace,
+                              workspace_bytes, (cudaStream_t)stream, d_out);
+}
+
+int sqz_segment_stats(int64_t n_chr, const int64_t* row_off, const int64_t* seg_off,
+                      const double* position, const double* adjusted_ratio,
+                      const double* depth_normal, const double* good_reads, const double* Af,
+                      const double* Bf, const unsigned char* is_het, const double* breaks_vect,
+                      double min_reads_baf, int weighted_mean, double* out) {
+  if (n_chr < 0) return fail(SQZ_ERR_ARG, "negative n_chr");
+  if (n_chr == 0) return SQZ_OK;
+  if (!row_off || !seg_off) return fail(SQZ_ERR_ARG, "offset arrays are null");
+  const int64_t N = row_off[n_chr], S = seg_off[n_chr];
+  if (row_off[0] != 0 || seg_off[0] != 0) return fail(SQZ_ERR_ARG, "offsets must start at 0");
+  for (int64_t c = 0; c < n_chr; ++c) {
+    if (row_off[c + 1] < row_off[c] || seg_off[c + 1] < seg_off[c])
+      return fail(SQZ_ERR_ARG, "offsets must be non-decreasing");
+    for (int64_t i = row_off[c] + 1; i < row_off[c + 1]; ++i)
+      if (position && position[i] < position[i - 1])
+        return fail(SQZ_ERR_ARG, "positions must be sorted inside each chromosome");
+    for (int64_t k = 2 * seg_off[c] + 1; k < 2 * seg_off[c + 1]; ++k)
+      if (breaks_vect && !(breaks_vect[k] > breaks_vect[k - 1]))
+        return fail(SQZ_ERR_ARG, "breaks must increase inside each chromosome (unique.breaks)");
+  }
+  if (S == 0) return SQZ_OK;
+  if ((N > 0 && (!position || !adjusted_ratio || !depth_normal || !good_reads || !Af || !Bf ||
+                 !is_het)) || !breaks_vect || !out)
+    return fail(SQZ_ERR_ARG, "null pointer argument");
+  int ndev = 0;
+  int rc = usable_devices(1, &ndev);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_mu);
+  int cur = 0;
+  SQZ_CUDA(cudaGetDevice(&cur));
+  DevCtx* c;
+  if ((rc = ctx_for(cur, &c))) return rc;
+  const size_t vb = a256((size_t)(N > 0 ? N : 1) * 8), hb = a256((size_t)(N > 0 ? N : 1));
+  const size_t ob = a256((size_t)(n_chr + 1) * 8), bb = a256((size_t)S * 16);
+  if ((rc = grow(&c->in, &c->in_cap, 6 * vb + hb + 2 * ob + bb))) return rc;
+  if ((rc = grow(&c->ws, &c->ws_cap, segment_stats_workspace_bytes(S)))) return rc;
+  if ((rc = grow(&c->out, &c->out_cap, (size_t)S * 48))) return rc;
+  char* p = (char*)c->in;
+  const double* src[6] = {position, adjusted_ratio, depth_normal, good_reads, Af, Bf};
+  const double* dv[6];
+  for (int k = 0; k < 6; ++k, p += vb) {
+    dv[k] = (const double*)p;
+    if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, src[k], (size_t)N * 8, cudaMemcpyHostToDevice, c->st));
+  }
+  const unsigned char* d_het = (const unsigned char*)p;
+  if (N > 0) SQZ_CUDA(cudaMemcpyAsync(p, is_het, (size_t)N, cudaMemcpyHostToDevice, c->st));
+  p += hb;
+  const int64_t* d_ro = (const int64_t*)p;
+  SQZ_CUDA(cudaMemcpyAsync(p, row_off, (size_t)(n_chr + 1) * 8, cudaMemcpyHostToDevice, c->st));
+  p += ob;
+  const int64_t* d_so = (const int64_t*)p;
+  SQZ_CUDA(cudaMemcpyAsync(p, seg_off, (size_t)(n_chr + 1) * 8, cudaMemcpyHostToDevice, c->st));
+  p += ob;
+  const double* d_brk = (const double*)p;
+  SQZ_CUDA(cudaMemcpyAsync(p, breaks_vect, (size_t)S * 16, cudaMemcpyHostToDevice, c->st));
+  rc = segment_stats_launch(n_chr, d_ro, d_so, S, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5],
+                            d_het, d_brk, min_reads_baf, weighted_mean, c->ws, c->ws_cap, c->st,
+                            (double*)c->out);
+  if (rc) {
+    cudaStreamSynchronize(c->st);
+    return rc;
+  }
+  SQZ_CUDA(cudaMemcpyAsync(out, c->out, (size_t)S * 48, cudaMemcpyDeviceToHost, c->st));
   SQZ_CUDA(cudaStreamSynchronize(c->st));
   return SQZ_OK;
 }

@@ -1,0 +1,506 @@
+// sqz_segstats.cu -- the per-segment statistics of segment.breaks (R/segments.R:113-198) and
+// the kernel-density mode of b_allele_freq (R/model.R:69-98): the step that turns the seqz
+// rows of a genome and its breakpoints into the segment table sequenza.fit consumes.
+//
+// Layout: the rows of all chromosomes concatenated (row_off[n_chr + 1]), sorted by position
+// inside each chromosome, one fp64 vector per seqz column plus a byte per row for
+// zygosity.normal == "het"; breaks_vect holds two values per segment, (start, end], the
+// output of unique.breaks (R/segments.R:133-139), increasing inside a chromosome.  A segment
+// is then a contiguous run of rows, found by two binary searches.
+//
+//   segstat_reduce_kernel  one CTA per segment, two passes over its rows (the second finds
+//                          them in L2): counts, the weighted sums, then the squared
+//                          deviations about the double-double means -- R's two-pass var();
+//                          also what the density needs (n, sum of good.reads, sd / min / max
+//                          of c(Bf, Af)).  49 bytes per row: HBM-bound.
+//   segstat_kde_kernel     one CTA per segment with at least two het positions:
+//                          quantile(type 7) by radix selection on the ordered bit patterns,
+//                          bw.nrd0, density.default's linear binning onto 512 points (64-bit
+//                          fixed-point shared-memory atomics: order-independent), the
+//                          correlation with dnorm summed directly (R does it by FFT), approx()
+//                          onto the 512 output points, and the highest local maximum.
+#include "sqz_common.cuh"
+#include "../../include/sequenza_b200.h"
+
+namespace sqz {
+
+namespace {
+constexpr int kSegThreads = 256;
+constexpr int kDensN = 512;  // density.default's n
+
+struct SegArgs {
+  int64_t n_chr;
+  const int64_t* row_off;  // [n_chr + 1]
+  const int64_t* seg_off;  // [n_chr + 1]
+  const double *pos, *ratio, *dnorm, *good, *Af, *Bf;
+  const unsigned char* het;
+  const double* brk;  // [2 * S]
+  double min_reads;
+  int weighted;
+  int64_t S;
+};
+
+// per segment, handed from the reduction to the density kernel
+struct SegMid {
+  int64_t lo, hi;   // its rows
+  int64_t nb;       // het rows with enough reads
+  double gsum;      // sum(good.reads) over them
+  double sdx;       // sd(c(Bf, Af))
+  double xmin, xmax, x0;  // range of c(Bf, Af) and its first element (Bf of the first row)
+};
+
+// ---- double-double helpers -------------------------------------------------------------
+struct D2 {
+  double hi, lo;
+};
+__device__ __forceinline__ D2 d2_add(D2 a, double x) {  // a + x, x finite
+  const double s = a.hi + x, bb = s - a.hi;
+  const double e = (a.hi - (s - bb)) + (x - bb);
+  const double lo = a.lo + e;
+  const double h = s + lo;
+  return D2{h, lo - (h - s)};
+}
+__device__ __forceinline__ D2 d2_merge(D2 a, D2 b) { return d2_add(d2_add(a, b.hi), b.lo); }
+__device__ __forceinline__ D2 d2_div(D2 a, double n) {  // a / n
+  const double q = a.hi / n;
+  const double r = fma(-q, n, a.hi) + a.lo;
+  const double q2 = r / n;
+  const double h = q + q2;
+  return D2{h, q2 - (h - q)};
+}
+
+template <int N>
+__device__ __forceinline__ void block_sum_d2(D2 (&v)[N], D2* red /* [N][8] */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    for (int off = 16; off; off >>= 1) {
+      D2 o;
+      o.hi = __shfl_xor_sync(0xffffffffu, v[k].hi, off);
+      o.lo = __shfl_xor_sync(0xffffffffu, v[k].lo, off);
+      v[k] = d2_merge(v[k], o);  // both partners compute hi + lo of the same pair in the same
+    }                            // order up to commutativity of the first addition
+    if (lane == 0) red[k * 8 + warp] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    D2 t = red[k * 8];
+    for (int w = 1; w < kSegThreads / 32; ++w) t = d2_merge(t, red[k * 8 + w]);
+    v[k] = t;
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ long long block_sum_ll(long long v, long long* red) {
+  for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  long long t = 0;
+  for (int w = 0; w < kSegThreads / 32; ++w) t += red[w];
+  __syncthreads();
+  return t;
+}
+
+__device__ __forceinline__ double block_minmax(double v, bool is_max, double* red) {
+  for (int off = 16; off; off >>= 1) {
+    const double o = __shfl_xor_sync(0xffffffffu, v, off);
+    v = is_max ? fmax(v, o) : fmin(v, o);
+  }
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = red[0];
+  for (int w = 1; w < kSegThreads / 32; ++w) t = is_max ? fmax(t, red[w]) : fmin(t, red[w]);
+  __syncthreads();
+  return t;
+}
+
+// first index in [a, b) whose position is > x (positions sorted)
+__device__ __forceinline__ int64_t upper_bound(const double* p, int64_t a, int64_t b, double x) {
+  while (a < b) {
+    const int64_t m = a + ((b - a) >> 1);
+    if (p[m] > x) b = m;
+    else a = m + 1;
+  }
+  return a;
+}
+}  // namespace
+
+// ---- reductions of one segment (R/segments.R:140-170) -----------------------------------
+__global__ void __launch_bounds__(kSegThreads)
+segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ out) {
+  __shared__ D2 red[8 * 8];
+  __shared__ long long redl[8];
+  __shared__ double redd[8];
+  __shared__ int64_t s_lo, s_hi;
+  const int64_t s = blockIdx.x;
+  if (threadIdx.x == 0) {
+    int64_t c = 0;
+    while (c + 1 < a.n_chr && a.seg_off[c + 1] <= s) ++c;
+    const int64_t r0 = a.row_off[c], r1 = a.row_off[c + 1];
+    // cut(position, breaks.vect): right-closed intervals (b0, b1] (R/segments.R:140-141)
+    s_lo = upper_bound(a.pos, r0, r1, a.brk[2 * s]);
+    s_hi = upper_bound(a.pos, s_lo, r1, a.brk[2 * s + 1]);
+  }
+  __syncthreads();
+  const int64_t lo = s_lo, hi = s_hi;
+  const bool W = a.weighted != 0;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+
+  // pass 1: counts and sums
+  D2 sum[6] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};  // rw, w.r, v, vb, good, x
+  long long nv = 0, nb = 0, nvb = 0, first = 0x7fffffffffffffffLL;
+  double vmin = INF, vmax = -INF, bmin = INF, bmax = -INF, xmin = INF, xmax = -INF;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kSegThreads) {
+    const double r = a.ratio[i];
+    double v;
+    if (W) {
+      const double wr = sqrt(a.dnorm[i]), rw = r * wr;  // R/segments.R:116-117
+      if (!isnan(rw)) sum[0] = d2_add(sum[0], rw);
+      if (!isnan(wr)) sum[1] = d2_add(sum[1], wr);
+      v = rw / wr;
+    } else {
+      v = r;
+    }
+    if (!isnan(v)) {
+      sum[2] = d2_add(sum[2], v);
+      ++nv;
+      vmin = fmin(vmin, v);
+      vmax = fmax(vmax, v);
+    }
+    const double g = a.good[i];
+    if (a.het[i] && g >= a.min_reads) {  // R/segments.R:128-129
+      const double bf = a.Bf[i], af = a.Af[i];
+      double vb = bf;
+      if (W) {
+        const double wb = sqrt(g);  // R/segments.R:118-119
+        vb = (bf * wb) / wb;
+      }
+      ++nb;
+      if (i < first) first = i;
+      if (!isnan(vb)) {
+        sum[3] = d2_add(sum[3], vb);
+        ++nvb;
+        bmin = fmin(bmin, vb);
+        bmax = fmax(bmax, vb);
+      }
+      sum[4] = d2_add(sum[4], g);
+      sum[5] = d2_add(d2_add(sum[5], bf), af);
+      xmin = fmin(xmin, fmin(bf, af));
+      xmax = fmax(xmax, fmax(bf, af));
+    }
+  }
+  block_sum_d2(sum, red);
+  nv = block_sum_ll(nv, redl);
+  nb = block_sum_ll(nb, redl);
+  nvb = block_sum_ll(nvb, redl);
+  vmin = block_minmax(vmin, false, redd);
+  vmax = block_minmax(vmax, true, redd);
+  bmin = block_minmax(bmin, false, redd);
+  bmax = block_minmax(bmax, true, redd);
+  xmin = block_minmax(xmin, false, redd);
+  xmax = block_minmax(xmax, true, redd);
+  {  // the first het row of the segment: x[1] of c(Bf, Af), bw.nrd0's last resort
+    long long f = first;
+    for (int off = 16; off; off >>= 1) f = min(f, __shfl_xor_sync(0xffffffffu, f, off));
+    if ((threadIdx.x & 31) == 0) redl[threadIdx.x >> 5] = f;
+    __syncthreads();
+    first = redl[0];
+    for (int w = 1; w < kSegThreads / 32; ++w) first = min(first, redl[w]);
+    __syncthreads();
+  }
+  const D2 mv = nv > 0 ? d2_div(sum[2], (double)nv) : D2{0, 0};
+  const D2 mb = nvb > 0 ? d2_div(sum[3], (double)nvb) : D2{0, 0};
+  const D2 mx = nb > 0 ? d2_div(sum[5], (double)(2 * nb)) : D2{0, 0};
+
+  // pass 2: squared deviations about the means (stats::var is two-pass)
+  D2 ss[3] = {{0, 0}, {0, 0}, {0, 0}};
+  auto dev2 = [](D2& acc, double x, const D2& m) {
+    const double d = (x - m.hi) - m.lo;
+    const double p = d * d;
+    acc = d2_add(d2_add(acc, p), fma(d, d, -p));
+  };
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kSegThreads) {
+    const double r = a.ratio[i];
+    double v = r;
+    if (W) {
+      const double wr = sqrt(a.dnorm[i]);
+      v = (r * wr) / wr;
+    }
+    if (!isnan(v)) dev2(ss[0], v, mv);
+    const double g = a.good[i];
+    if (a.het[i] && g >= a.min_reads) {
+      const double bf = a.Bf[i], af = a.Af[i];
+      double vb = bf;
+      if (W) {
+        const double wb = sqrt(g);
+        vb = (bf * wb) / wb;
+      }
+      if (!isnan(vb)) dev2(ss[1], vb, mb);
+      dev2(ss[2], bf, mx);
+      dev2(ss[2], af, mx);
+    }
+  }
+  block_sum_d2(ss, red);
+  if (threadIdx.x != 0) return;
+  auto sd = [](const D2& q, long long n, double mn, double mxv) {
+    if (n < 2) return na_real();
+    if (mn == mxv) return 0.0;  // identical values: exactly zero, as the two-pass var gives
+    return sqrt((q.hi + q.lo) / (double)(n - 1));
+  };
+  const int64_t S = a.S;
+  double bfo = na_real();
+  if (nb == 1) bfo = a.Bf[first];  // length(Bf) == 1 (R/model.R:93-94)
+  out[0 * S + s] = bfo;            // nb >= 2: the density kernel fills it in
+  out[1 * S + s] = (double)nb;
+  out[2 * S + s] = sd(ss[1], nvb, bmin, bmax);
+  out[3 * S + s] = W ? (sum[0].hi + sum[0].lo) / (sum[1].hi + sum[1].lo)
+                     : (nv > 0 ? mv.hi + mv.lo : __longlong_as_double(0x7FF8000000000000LL));
+  out[4 * S + s] = (double)(hi - lo);
+  out[5 * S + s] = sd(ss[0], nv, vmin, vmax);
+  SegMid m;
+  m.lo = lo;
+  m.hi = hi;
+  m.nb = nb;
+  m.gsum = sum[4].hi + sum[4].lo;
+  m.sdx = nb >= 1 ? sd(ss[2], 2 * nb, xmin, xmax) : 0.0;
+  m.xmin = xmin;
+  m.xmax = xmax;
+  m.x0 = nb >= 1 ? a.Bf[first] : 0.0;
+  mid[s] = m;
+}
+
+// ---- the mode of the kernel density of c(Bf, Af) (R/model.R:69-88) ------------------------
+namespace {
+// doubles as unsigned keys with the same order
+__device__ __forceinline__ unsigned long long dkey(double x) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double dunkey(unsigned long long k) {
+  const unsigned long long b = (k >> 63) ? (k & 0x7FFFFFFFFFFFFFFFULL) : ~k;
+  return __longlong_as_double((long long)b);
+}
+
+// stats::dnorm(x, 0, sigma) (nmath/dnorm.c, R >= 3.1)
+__device__ __forceinline__ double r_dnorm(double x, double sigma) {
+  const double k = 0.398942280401432677939946059934;
+  x = fabs(x / sigma);
+  if (x < 5) return k * exp(-0.5 * x * x) / sigma;
+  if (x > 38.56804181549334) return 0.;  // sqrt(-2 ln2 (DBL_MIN_EXP + 1 - DBL_MANT_DIG))
+  const double x1 = ldexp(nearbyint(ldexp(x, 16)), -16);
+  const double x2 = x - x1;
+  return k / sigma * (exp(-0.5 * x1 * x1) * exp((-0.5 * x2 - x1) * x2));
+}
+}  // namespace
+
+__global__ void __launch_bounds__(kSegThreads)
+segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, double* __restrict__ out) {
+  __shared__ unsigned hist[256];
+  __shared__ unsigned long long s_prefix;
+  __shared__ long long s_rank;
+  __shared__ unsigned long long ybin[kDensN + 1];  // 2^-62 fixed point
+  __shared__ double K[kDensN + 1], kords[kDensN], gy[kDensN];
+  __shared__ double s_q[4];
+  const int64_t s = blockIdx.x;
+  const SegMid m = mid[s];
+  if (m.nb < 2) return;  // 0: NA, 1: Bf itself -- written by the reduction kernel
+  const int tid = threadIdx.x;
+  const int64_t N = 2 * m.nb;
+
+  // x = c(Bf, Af) of the het rows; the k-th smallest (0-based) by radix selection on the
+  // ordered bit patterns, 8 bits a pass, most significant first
+  auto select = [&](int64_t k) {
+    __syncthreads();  // everyone has read the previous selection's result
+    if (tid == 0) {
+      s_prefix = 0;
+      s_rank = k;
+    }
+    for (int shift = 56; shift >= 0; shift -= 8) {
+      hist[tid] = 0;
+      __syncthreads();
+      const unsigned long long prefix = s_prefix;
+      const unsigned long long mask = shift == 56 ? 0ULL : (~0ULL << (shift + 8));
+      for (int64_t i = m.lo + tid; i < m.hi; i += kSegThreads) {
+        if (a.het[i] && a.good[i] >= a.min_reads) {
+          const unsigned long long k0 = dkey(a.Bf[i]), k1 = dkey(a.Af[i]);
+          if ((k0 & mask) == prefix) atomicAdd(&hist[(k0 >> shift) & 255], 1u);
+          if ((k1 & mask) == prefix) atomicAdd(&hist[(k1 >> shift) & 255], 1u);
+        }
+      }
+      __syncthreads();
+      if (tid == 0) {
+        long long r = s_rank;
+        int b = 0;
+        while (b < 255 && r >= (long long)hist[b]) {
+          r -= hist[b];
+          ++b;
+        }
+        s_rank = r;
+        s_prefix = prefix | ((unsigned long long)b << shift);
+      }
+      __syncthreads();
+    }
+    return dunkey(s_prefix);
+  };
+  // quantile(x, c(.25, .75), type = 7): index = 1 + (n - 1) p; (1 - h) x[lo] + h x[hi]
+  for (int q = 0; q < 2; ++q) {
+    const double index = 1 + (double)(N - 1) * (q == 0 ? 0.25 : 0.75);
+    const double fl = floor(index), ce = ceil(index);
+    const double xl = select((int64_t)fl - 1);
+    const double xh = ce == fl ? xl : select((int64_t)ce - 1);
+    if (tid == 0) {
+      double v = xl;
+      if (index > fl && xh != xl) {
+        const double h = index - fl;
+        v = (1 - h) * xl + h * xh;
+      }
+      s_q[q] = v;
+    }
+  }
+  __syncthreads();
+  // bw.nrd0: 0.9 min(sd, IQR / 1.34) n^-0.2, with its fall-backs for a zero spread
+  double lo_ = fmin(m.sdx, (s_q[1] - s_q[0]) / 1.34);
+  if (!(lo_ != 0)) {
+    lo_ = m.sdx;
+    if (!(lo_ != 0)) {
+      lo_ = fabs(m.x0);
+      if (!(lo_ != 0)) lo_ = 1.;
+    }
+  }
+  const double bw = 0.9 * lo_ * pow((double)N, -0.2);
+  const double from = m.xmin - 3 * bw, to = m.xmax + 3 * bw;  // cut = 3
+  const double lo = from - 4 * bw, up = to + 4 * bw;
+  const int n = kDensN;
+
+  // BinDist: linear binning of the weights good.reads / (2 sum(good.reads)) onto n points
+  for (int j = tid; j <= n; j += kSegThreads) ybin[j] = 0;
+  for (int d = tid; d <= n; d += kSegThreads) K[d] = r_dnorm(d * (2 * (up - lo) / (2 * n - 1)), bw);
+  __syncthreads();
+  {
+    const double xdelta = (up - lo) / (n - 1), two_sum = 2 * m.gsum;
+    const double SC = 4611686018427387904.0;  // 2^62
+    for (int64_t i = m.lo + tid; i < m.hi; i += kSegThreads) {
+      const double g = a.good[i];
+      if (a.het[i] && g >= a.min_reads) {
+        const double w = g / two_sum;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const double x = h == 0 ? a.Bf[i] : a.Af[i];
+          if (!isfinite(x)) continue;
+          const double xpos = (x - lo) / xdelta;
+          const int ix = (int)floor(xpos);
+          const double fx = xpos - ix;
+          if (0 <= ix && ix <= n - 2) {
+            atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+            atomicAdd(&ybin[ix + 1], (unsigned long long)(w * fx * SC + 0.5));
+          } else if (ix == -1) {
+            atomicAdd(&ybin[0], (unsigned long long)(w * fx * SC + 0.5));
+          } else if (ix == n - 1) {
+            atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // the correlation of the bins with dnorm(kords) (R: fft(fft(y) * Conj(fft(kords)))): the
+  // kernel is symmetric and only the first n bins are occupied, so K[|m - j|] is all of it
+  for (int j = tid; j < n; j += kSegThreads) {
+    double acc = 0.;
+    for (int mm = 0; mm < n; ++mm) {
+      const unsigned long long yb = ybin[mm];
+      if (yb) acc += ((double)yb * (1.0 / 4611686018427387904.0)) * K[mm > j ? mm - j : j - mm];
+    }
+    kords[j] = acc > 0 ? acc : 0;
+  }
+  __syncthreads();
+  // approx(xords, kords, seq(from, to, length.out = n))
+  {
+    const double byx = (up - lo) / (n - 1), byg = (to - from) / (n - 1);
+    for (int j = tid; j < n; j += kSegThreads) {
+      const double v = j == n - 1 ? to : from + j * byg;
+      int i = 0, jj = n - 1;
+      auto xo = [&](int t) { return t == n - 1 ? up : lo + t * byx; };
+      while (i < jj - 1) {
+        const int ij = (i + jj) / 2;
+        if (v < xo(ij)) jj = ij;
+        else i = ij;
+      }
+      double y;
+      if (v == xo(jj)) y = kords[jj];
+      else if (v == xo(i)) y = kords[i];
+      else y = kords[i] + (kords[jj] - kords[i]) * ((v - xo(i)) / (xo(jj) - xo(i)));
+      gy[j] = y;
+    }
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  // the highest local maximum, first on ties (R/model.R:73-85); a top that is a run of equal
+  // values counts at its first point (R's FFT noise makes one of them the maximum; after the
+  // fold about 0.5 that is the same number to rounding)
+  int best = -1, cand = -1;
+  for (int j = 0; j + 1 < n; ++j) {
+    const double d = gy[j + 1] - gy[j];
+    if (d > 0) {
+      cand = j + 1;
+    } else if (d < 0) {
+      if (cand >= 0 && (best < 0 || gy[cand] > gy[best])) best = cand;
+      cand = -1;
+    }
+  }
+  if (best < 0) {
+    for (int j = 1; j < n - 1; ++j) {
+      const double d0 = gy[j] - gy[j - 1], d1 = gy[j + 1] - gy[j];
+      const int s0 = (d0 > 0) - (d0 < 0), s1 = (d1 > 0) - (d1 < 0);
+      if (s1 - s0 == -1 && (best < 0 || gy[j] > gy[best])) best = j;
+    }
+  }
+  double b_val = na_real();
+  if (best >= 0) {
+    b_val = best == n - 1 ? to : from + best * ((to - from) / (n - 1));
+    if (b_val > 0.5) b_val = 1 - b_val;  // R/model.R:86-88
+  }
+  out[s] = b_val;  // column 0: Bf
+}
+
+// ---- host side ---------------------------------------------------------------------------
+size_t segment_stats_workspace_bytes(int64_t n_seg) {
+  return ((size_t)(n_seg > 0 ? n_seg : 1) * sizeof(SegMid) + 255) & ~(size_t)255;
+}
+
+int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
+                         int64_t n_seg, const double* d_pos, const double* d_ratio,
+                         const double* d_dnorm, const double* d_good, const double* d_Af,
+                         const double* d_Bf, const unsigned char* d_het, const double* d_brk,
+                         double min_reads_baf, int weighted_mean, void* workspace,
+                         size_t workspace_bytes, cudaStream_t st, double* d_out) {
+  if (n_chr < 0 || n_seg < 0) return fail(SQZ_ERR_ARG, "negative size");
+  if (n_seg == 0) return SQZ_OK;
+  if (n_seg > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "more than 2^31-1 segments");
+  if (!workspace || workspace_bytes < segment_stats_workspace_bytes(n_seg))
+    return fail(SQZ_ERR_SIZE, "segment-statistics workspace too small");
+  SegArgs a;
+  a.n_chr = n_chr;
+  a.row_off = d_row_off;
+  a.seg_off = d_seg_off;
+  a.pos = d_pos;
+  a.ratio = d_ratio;
+  a.dnorm = d_dnorm;
+  a.good = d_good;
+  a.Af = d_Af;
+  a.Bf = d_Bf;
+  a.het = d_het;
+  a.brk = d_brk;
+  a.min_reads = min_reads_baf;
+  a.weighted = weighted_mean ? 1 : 0;
+  a.S = n_seg;
+  SegMid* mid = (SegMid*)workspace;
+  segstat_reduce_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, d_out);
+  SQZ_CUDA(cudaGetLastError());
+  segstat_kde_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, d_out);
+  SQZ_CUDA(cudaGetLastError());
+  return SQZ_OK;
+}
+
+}  // namespace sqz

@@ -106,7 +106,7 @@ def synth_seqz(n_chr=3, rows_per_chr=4000, segs_per_chr=7, seed=1, het_frac=0.3,
     row_off, seg_off = [0], [0]
     for _ in range(n_chr):
         cb = []
-        p = np.sort(rng.choice(np.arange(1, 40 * rows_per_chr), rows_per_chr, replace=False))
+        p = np.cumsum(rng.integers(1, 80, rows_per_chr))  # sorted, distinct positions
         cuts = np.sort(rng.choice(np.arange(5, rows_per_chr - 5), segs_per_chr - 1,
                                   replace=False))
         edges = np.concatenate([[0], cuts, [rows_per_chr - 1]])
