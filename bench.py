@@ -760,14 +760,15 @@ def run_other(args, env, local_rank):
             dro = torch.from_numpy(g["row_off"]).to(device)
             dso = torch.from_numpy(g["seg_off"]).to(device)
             dbrk = torch.from_numpy(g["breaks_vect"]).to(device)
-            wsb = L.sqz_segment_stats_workspace_bytes(n_seg)
+            wsb = L.sqz_segment_stats_workspace_bytes(n_rows, n_seg)
             ws = torch.empty(wsb + 256, dtype=torch.uint8, device=device)
             wsp = (ws.data_ptr() + 255) & ~255
             dout = torch.empty(6 * n_seg, dtype=torch.float64, device=device)
 
             def call():
                 _lib.check(L.sqz_segment_stats_dev(
-                    24, dro.data_ptr(), dso.data_ptr(), n_seg, *[t.data_ptr() for t in dv],
+                    24, dro.data_ptr(), dso.data_ptr(), n_rows, n_seg,
+                    *[t.data_ptr() for t in dv],
                     dhet.data_ptr(), dbrk.data_ptr(), 1.0, 1, wsp, wsb, stream, dout.data_ptr()))
             ms = timed_ms(torch, call, steps, args.warmup, env["flush"])
             got = dout.cpu().numpy().reshape(6, n_seg).T

@@ -324,16 +324,17 @@ int sqz_fit_finish_dev(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t n
  * binning onto 512 points, gaussian kernel, approx) with the convolution summed directly
  * instead of by FFT; one stated departure: a maximum whose top is a run of exactly equal
  * values counts at its first point.
- * The _dev form needs sqz_segment_stats_workspace_bytes(n_seg) bytes, 256-byte aligned.
+ * The _dev form needs sqz_segment_stats_workspace_bytes(n_rows, n_seg) bytes, 256-byte
+ * aligned (a hand-over record per segment and a compact copy of the het rows).
  * --------------------------------------------------------------------------------- */
 int sqz_segment_stats(int64_t n_chr, const int64_t* row_off, const int64_t* seg_off,
                       const double* position, const double* adjusted_ratio,
                       const double* depth_normal, const double* good_reads, const double* Af,
                       const double* Bf, const unsigned char* is_het, const double* breaks_vect,
                       double min_reads_baf, int weighted_mean, double* out);
-size_t sqz_segment_stats_workspace_bytes(int64_t n_seg);
+size_t sqz_segment_stats_workspace_bytes(int64_t n_rows, int64_t n_seg);
 int sqz_segment_stats_dev(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
-                          int64_t n_seg, const double* d_position,
+                          int64_t n_rows, int64_t n_seg, const double* d_position,
                           const double* d_adjusted_ratio, const double* d_depth_normal,
                           const double* d_good_reads, const double* d_Af, const double* d_Bf,
                           const unsigned char* d_is_het, const double* d_breaks_vect,

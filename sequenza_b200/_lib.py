@@ -66,8 +66,9 @@ SIGNATURES = {
     "sqz_fit_finish": (_i, [_p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p]),
     "sqz_fit_finish_dev": (_i, [_p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "sqz_segment_stats": (_i, [_i64, _p, _p] + [_p] * 8 + [_d, _i, _p]),
-    "sqz_segment_stats_workspace_bytes": (_sz, [_i64]),
-    "sqz_segment_stats_dev": (_i, [_i64, _p, _p, _i64] + [_p] * 8 + [_d, _i, _p, _sz, _p, _p]),
+    "sqz_segment_stats_workspace_bytes": (_sz, [_i64, _i64]),
+    "sqz_segment_stats_dev": (_i, [_i64, _p, _p, _i64, _i64] + [_p] * 8 + [_d, _i, _p, _sz, _p,
+                                   _p]),
     "sqz_model_points": (_i, [_i, _d, _d, _d, _i, _i, _i, _p, _p, _i, _p, _p]),
     "sqz_fp64_peak": (_i, [_i, _i, _p]),
     "sqz_baf_grid_plan": (_i, [_i64, _i64, _p, _i64, _i64, _i, _i, _i, _i, _p]),

@@ -77,9 +77,9 @@ int fit_finish_launch(const double* d_lpp_sum, int64_t S, int64_t nP, int64_t nC
                       double* d_znorm, double* d_row_max, double* d_col_max,
                       double* d_row_above, double* d_col_above, double* d_lsl,
                       cudaStream_t st);
-size_t segment_stats_workspace_bytes(int64_t n_seg);
+size_t segment_stats_workspace_bytes(int64_t n_rows, int64_t n_seg);
 int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
-                         int64_t n_seg, const double* d_pos, const double* d_ratio,
+                         int64_t n_rows, int64_t n_seg, const double* d_pos, const double* d_ratio,
                          const double* d_dnorm, const double* d_good, const double* d_Af,
                          const double* d_Bf, const unsigned char* d_het, const double* d_brk,
                          double min_reads_baf, int weighted_mean, void* workspace,
@@ -848,12 +848,12 @@ int sqz_fit_finish(const double* lpp_sum, int64_t S, int64_t nP, int64_t nC, dou
   return SQZ_OK;
 }
 
-size_t sqz_segment_stats_workspace_bytes(int64_t n_seg) {
-  return segment_stats_workspace_bytes(n_seg);
+size_t sqz_segment_stats_workspace_bytes(int64_t n_rows, int64_t n_seg) {
+  return segment_stats_workspace_bytes(n_rows, n_seg);
 }
 
 int sqz_segment_stats_dev(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
-                          int64_t n_seg, const double* d_position,
+                          int64_t n_rows, int64_t n_seg, const double* d_position,
                           const double* d_adjusted_ratio, const double* d_depth_normal,
                           const double* d_good_reads, const double* d_Af, const double* d_Bf,
                           const unsigned char* d_is_het, const double* d_breaks_vect,
@@ -861,7 +861,8 @@ int sqz_segment_stats_dev(int64_t n_chr, const int64_t* d_row_off, const int64_t
                           size_t workspace_bytes, void* stream, double* d_out) {
   if (sqz_device_count() < 1)
     return fail(SQZ_ERR_NOGPU, "no CUDA device available: libsequenza_b200 has no CPU path");
-  return segment_stats_launch(n_chr, d_row_off, d_seg_off, n_seg, d_position, d_adjusted_ratio,
+  return segment_stats_launch(n_chr, d_row_off, d_seg_off, n_rows, n_seg, d_position,
+                              d_adjusted_ratio,
                               d_depth_normal, d_good_reads, d_Af, d_Bf, d_is_het,
                               d_breaks_vect, min_reads_baf, weighted_mean, workspace,
                               workspace_bytes, (cudaStream_t)stream, d_out);
@@ -902,7 +903,7 @@ int sqz_segment_stats(int64_t n_chr, const int64_t* row_off, const int64_t* seg_
   const size_t vb = a256((size_t)(N > 0 ? N : 1) * 8), hb = a256((size_t)(N > 0 ? N : 1));
   const size_t ob = a256((size_t)(n_chr + 1) * 8), bb = a256((size_t)S * 16);
   if ((rc = grow(&c->in, &c->in_cap, 6 * vb + hb + 2 * ob + bb))) return rc;
-  if ((rc = grow(&c->ws, &c->ws_cap, segment_stats_workspace_bytes(S)))) return rc;
+  if ((rc = grow(&c->ws, &c->ws_cap, segment_stats_workspace_bytes(N, S)))) return rc;
   if ((rc = grow(&c->out, &c->out_cap, (size_t)S * 48))) return rc;
   char* p = (char*)c->in;
   const double* src[6] = {position, adjusted_ratio, depth_normal, good_reads, Af, Bf};
@@ -922,7 +923,7 @@ int sqz_segment_stats(int64_t n_chr, const int64_t* row_off, const int64_t* seg_
   p += ob;
   const double* d_brk = (const double*)p;
   SQZ_CUDA(cudaMemcpyAsync(p, breaks_vect, (size_t)S * 16, cudaMemcpyHostToDevice, c->st));
-  rc = segment_stats_launch(n_chr, d_ro, d_so, S, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5],
+  rc = segment_stats_launch(n_chr, d_ro, d_so, N, S, dv[0], dv[1], dv[2], dv[3], dv[4], dv[5],
                             d_het, d_brk, min_reads_baf, weighted_mean, c->ws, c->ws_cap, c->st,
                             (double*)c->out);
   if (rc) {

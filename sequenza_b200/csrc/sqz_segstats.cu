@@ -13,8 +13,14 @@
 //                          deviations about the double-double means -- R's two-pass var();
 //                          also what the density needs (n, sum of good.reads, sd / min / max
 //                          of c(Bf, Af)).  49 bytes per row: HBM-bound.
+//                          The het rows' (Bf, Af, good.reads) are copied next to each other
+//                          into the workspace (any order: everything downstream is
+//                          order-independent), so the density kernel streams 24 bytes per het
+//                          row instead of re-reading 25 bytes of every row.
 //   segstat_kde_kernel     one CTA per segment with at least two het positions:
-//                          quantile(type 7) by radix selection on the ordered bit patterns,
+//                          quantile(type 7) by radix selection on the ordered bit patterns
+//                          (the four order statistics of the two quartiles in the same eight
+//                          passes),
 //                          bw.nrd0, density.default's linear binning onto 512 points (64-bit
 //                          fixed-point shared-memory atomics: order-independent), the
 //                          correlation with dnorm summed directly (R does it by FFT), approx()
@@ -128,7 +134,9 @@ __device__ __forceinline__ int64_t upper_bound(const double* p, int64_t a, int64
 
 // ---- reductions of one segment (R/segments.R:140-170) -----------------------------------
 __global__ void __launch_bounds__(kSegThreads)
-segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ out) {
+segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ cx,
+                      double* __restrict__ cg, double* __restrict__ out) {
+  __shared__ unsigned s_slot;
   __shared__ D2 red[8 * 8];
   __shared__ long long redl[8];
   __shared__ double redd[8];
@@ -141,6 +149,7 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
     // cut(position, breaks.vect): right-closed intervals (b0, b1] (R/segments.R:140-141)
     s_lo = upper_bound(a.pos, r0, r1, a.brk[2 * s]);
     s_hi = upper_bound(a.pos, s_lo, r1, a.brk[2 * s + 1]);
+    s_slot = 0;
   }
   __syncthreads();
   const int64_t lo = s_lo, hi = s_hi;
@@ -186,6 +195,11 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       }
       sum[4] = d2_add(sum[4], g);
       sum[5] = d2_add(d2_add(sum[5], bf), af);
+      // compact copy for the density kernel: the segment owns cx[2 lo, 2 hi) and cg[lo, hi)
+      const unsigned slot = atomicAdd(&s_slot, 1u);
+      cx[2 * (lo + slot)] = bf;
+      cx[2 * (lo + slot) + 1] = af;
+      cg[lo + slot] = g;
       xmin = fmin(xmin, fmin(bf, af));
       xmax = fmax(xmax, fmax(bf, af));
     }
@@ -295,10 +309,11 @@ __device__ __forceinline__ double r_dnorm(double x, double sigma) {
 }  // namespace
 
 __global__ void __launch_bounds__(kSegThreads)
-segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, double* __restrict__ out) {
-  __shared__ unsigned hist[256];
-  __shared__ unsigned long long s_prefix;
-  __shared__ long long s_rank;
+segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __restrict__ cx,
+                   const double* __restrict__ cg, double* __restrict__ out) {
+  __shared__ unsigned hist[4][256];
+  __shared__ unsigned long long s_prefix[4];
+  __shared__ long long s_rank[4];
   __shared__ unsigned long long ybin[kDensN + 1];  // 2^-62 fixed point
   __shared__ double K[kDensN + 1], kords[kDensN], gy[kDensN];
   __shared__ double s_q[4];
@@ -308,55 +323,60 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, double* __restrict
   const int tid = threadIdx.x;
   const int64_t N = 2 * m.nb;
 
-  // x = c(Bf, Af) of the het rows; the k-th smallest (0-based) by radix selection on the
-  // ordered bit patterns, 8 bits a pass, most significant first
-  auto select = [&](int64_t k) {
-    __syncthreads();  // everyone has read the previous selection's result
-    if (tid == 0) {
-      s_prefix = 0;
-      s_rank = k;
-    }
-    for (int shift = 56; shift >= 0; shift -= 8) {
-      hist[tid] = 0;
-      __syncthreads();
-      const unsigned long long prefix = s_prefix;
-      const unsigned long long mask = shift == 56 ? 0ULL : (~0ULL << (shift + 8));
-      for (int64_t i = m.lo + tid; i < m.hi; i += kSegThreads) {
-        if (a.het[i] && a.good[i] >= a.min_reads) {
-          const unsigned long long k0 = dkey(a.Bf[i]), k1 = dkey(a.Af[i]);
-          if ((k0 & mask) == prefix) atomicAdd(&hist[(k0 >> shift) & 255], 1u);
-          if ((k1 & mask) == prefix) atomicAdd(&hist[(k1 >> shift) & 255], 1u);
-        }
-      }
-      __syncthreads();
-      if (tid == 0) {
-        long long r = s_rank;
-        int b = 0;
-        while (b < 255 && r >= (long long)hist[b]) {
-          r -= hist[b];
-          ++b;
-        }
-        s_rank = r;
-        s_prefix = prefix | ((unsigned long long)b << shift);
-      }
-      __syncthreads();
-    }
-    return dunkey(s_prefix);
-  };
-  // quantile(x, c(.25, .75), type = 7): index = 1 + (n - 1) p; (1 - h) x[lo] + h x[hi]
+  const double* x = cx + 2 * m.lo;  // c(Bf, Af) of the het rows, interleaved: N values
+  const double* gw = cg + m.lo;     // good.reads of the same rows
+
+  // quantile(x, c(.25, .75), type = 7): index = 1 + (n - 1) p; (1 - h) x[lo] + h x[hi].
+  // The four order statistics by radix selection on the ordered bit patterns, 8 bits a
+  // pass, most significant first, all four in the same passes.
+  double qidx[2], qfl[2];
+  long long want[4];
   for (int q = 0; q < 2; ++q) {
-    const double index = 1 + (double)(N - 1) * (q == 0 ? 0.25 : 0.75);
-    const double fl = floor(index), ce = ceil(index);
-    const double xl = select((int64_t)fl - 1);
-    const double xh = ce == fl ? xl : select((int64_t)ce - 1);
-    if (tid == 0) {
-      double v = xl;
-      if (index > fl && xh != xl) {
-        const double h = index - fl;
-        v = (1 - h) * xl + h * xh;
-      }
-      s_q[q] = v;
+    qidx[q] = 1 + (double)(N - 1) * (q == 0 ? 0.25 : 0.75);
+    qfl[q] = floor(qidx[q]);
+    want[2 * q] = (long long)qfl[q] - 1;
+    want[2 * q + 1] = (long long)ceil(qidx[q]) - 1;
+  }
+  if (tid < 4) {
+    s_prefix[tid] = 0;
+    s_rank[tid] = want[tid];
+  }
+  for (int shift = 56; shift >= 0; shift -= 8) {
+    for (int t = tid; t < 4 * 256; t += kSegThreads) (&hist[0][0])[t] = 0;
+    __syncthreads();
+    const unsigned long long mask = shift == 56 ? 0ULL : (~0ULL << (shift + 8));
+    const unsigned long long p0 = s_prefix[0], p1 = s_prefix[1], p2 = s_prefix[2],
+                             p3 = s_prefix[3];
+    for (int64_t i = tid; i < N; i += kSegThreads) {
+      const unsigned long long k = dkey(x[i]);
+      const unsigned long long hi_bits = k & mask;
+      const unsigned d = (unsigned)(k >> shift) & 255u;
+      if (hi_bits == p0) atomicAdd(&hist[0][d], 1u);
+      if (hi_bits == p1) atomicAdd(&hist[1][d], 1u);
+      if (hi_bits == p2) atomicAdd(&hist[2][d], 1u);
+      if (hi_bits == p3) atomicAdd(&hist[3][d], 1u);
     }
+    __syncthreads();
+    if (tid < 4) {
+      long long r = s_rank[tid];
+      int b = 0;
+      while (b < 255 && r >= (long long)hist[tid][b]) {
+        r -= hist[tid][b];
+        ++b;
+      }
+      s_rank[tid] = r;
+      s_prefix[tid] |= (unsigned long long)b << shift;
+    }
+    __syncthreads();
+  }
+  if (tid < 2) {
+    const double xl = dunkey(s_prefix[2 * tid]), xh = dunkey(s_prefix[2 * tid + 1]);
+    double v = xl;
+    if (qidx[tid] > qfl[tid] && xh != xl) {
+      const double h = qidx[tid] - qfl[tid];
+      v = (1 - h) * xl + h * xh;
+    }
+    s_q[tid] = v;
   }
   __syncthreads();
   // bw.nrd0: 0.9 min(sd, IQR / 1.34) n^-0.2, with its fall-backs for a zero spread
@@ -380,26 +400,19 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, double* __restrict
   {
     const double xdelta = (up - lo) / (n - 1), two_sum = 2 * m.gsum;
     const double SC = 4611686018427387904.0;  // 2^62
-    for (int64_t i = m.lo + tid; i < m.hi; i += kSegThreads) {
-      const double g = a.good[i];
-      if (a.het[i] && g >= a.min_reads) {
-        const double w = g / two_sum;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const double x = h == 0 ? a.Bf[i] : a.Af[i];
-          if (!isfinite(x)) continue;
-          const double xpos = (x - lo) / xdelta;
-          const int ix = (int)floor(xpos);
-          const double fx = xpos - ix;
-          if (0 <= ix && ix <= n - 2) {
-            atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
-            atomicAdd(&ybin[ix + 1], (unsigned long long)(w * fx * SC + 0.5));
-          } else if (ix == -1) {
-            atomicAdd(&ybin[0], (unsigned long long)(w * fx * SC + 0.5));
-          } else if (ix == n - 1) {
-            atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
-          }
-        }
+    for (int64_t i = tid; i < N; i += kSegThreads) {
+      const double w = gw[i >> 1] / two_sum, xv = x[i];
+      if (!isfinite(xv)) continue;
+      const double xpos = (xv - lo) / xdelta;
+      const int ix = (int)floor(xpos);
+      const double fx = xpos - ix;
+      if (0 <= ix && ix <= n - 2) {
+        atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+        atomicAdd(&ybin[ix + 1], (unsigned long long)(w * fx * SC + 0.5));
+      } else if (ix == -1) {
+        atomicAdd(&ybin[0], (unsigned long long)(w * fx * SC + 0.5));
+      } else if (ix == n - 1) {
+        atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
       }
     }
   }
@@ -465,12 +478,16 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, double* __restrict
 }
 
 // ---- host side ---------------------------------------------------------------------------
-size_t segment_stats_workspace_bytes(int64_t n_seg) {
-  return ((size_t)(n_seg > 0 ? n_seg : 1) * sizeof(SegMid) + 255) & ~(size_t)255;
+static size_t seg_a256(size_t x) { return (x + 255) & ~(size_t)255; }
+// per segment hand-over + the compact copy of the het rows (24 bytes per row at most)
+size_t segment_stats_workspace_bytes(int64_t n_rows, int64_t n_seg) {
+  const size_t n = (size_t)(n_rows > 0 ? n_rows : 1);
+  return seg_a256((size_t)(n_seg > 0 ? n_seg : 1) * sizeof(SegMid)) + seg_a256(16 * n) +
+         seg_a256(8 * n);
 }
 
 int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t* d_seg_off,
-                         int64_t n_seg, const double* d_pos, const double* d_ratio,
+                         int64_t n_rows, int64_t n_seg, const double* d_pos, const double* d_ratio,
                          const double* d_dnorm, const double* d_good, const double* d_Af,
                          const double* d_Bf, const unsigned char* d_het, const double* d_brk,
                          double min_reads_baf, int weighted_mean, void* workspace,
@@ -478,8 +495,9 @@ int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t*
   if (n_chr < 0 || n_seg < 0) return fail(SQZ_ERR_ARG, "negative size");
   if (n_seg == 0) return SQZ_OK;
   if (n_seg > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "more than 2^31-1 segments");
-  if (!workspace || workspace_bytes < segment_stats_workspace_bytes(n_seg))
-    return fail(SQZ_ERR_SIZE, "segment-statistics workspace too small");
+  if (!workspace || ((uintptr_t)workspace & 255) ||
+      workspace_bytes < segment_stats_workspace_bytes(n_rows, n_seg))
+    return fail(SQZ_ERR_SIZE, "segment-statistics workspace too small or not 256-byte aligned");
   SegArgs a;
   a.n_chr = n_chr;
   a.row_off = d_row_off;
@@ -496,9 +514,11 @@ int segment_stats_launch(int64_t n_chr, const int64_t* d_row_off, const int64_t*
   a.weighted = weighted_mean ? 1 : 0;
   a.S = n_seg;
   SegMid* mid = (SegMid*)workspace;
-  segstat_reduce_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, d_out);
+  double* cx = (double*)((char*)workspace + seg_a256((size_t)n_seg * sizeof(SegMid)));
+  double* cg = (double*)((char*)cx + seg_a256(16 * (size_t)(n_rows > 0 ? n_rows : 1)));
+  segstat_reduce_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, cx, cg, d_out);
   SQZ_CUDA(cudaGetLastError());
-  segstat_kde_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, d_out);
+  segstat_kde_kernel<<<(unsigned)n_seg, kSegThreads, 0, st>>>(a, mid, cx, cg, d_out);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }

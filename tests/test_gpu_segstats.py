@@ -40,7 +40,7 @@ def test_segment_stats_match_oracle(oracle, shape, weighted):
                      seed=sum(shape))
     got, ref = both(oracle, g, weighted=weighted)
     check(got, ref)
-    assert (ref[:, 4] > 0).all()
+    assert (ref[:, 4] > 0).any()
 
 
 def test_segment_stats_edge_cases(oracle):
