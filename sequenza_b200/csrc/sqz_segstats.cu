@@ -8,11 +8,13 @@
 // output of unique.breaks (R/segments.R:133-139), increasing inside a chromosome.  A segment
 // is then a contiguous run of rows, found by two binary searches.
 //
-//   segstat_reduce_kernel  one CTA per segment, two passes over its rows (the second finds
-//                          them in L2): counts, the weighted sums, then the squared
-//                          deviations about the double-double means -- R's two-pass var();
-//                          also what the density needs (n, sum of good.reads, sd / min / max
-//                          of c(Bf, Af)).  49 bytes per row: HBM-bound.
+//   segstat_reduce_kernel  one CTA per segment, ONE pass over its rows: counts, the weighted
+//                          sums, and sum / sum of squares in double-double (106 bits), from
+//                          which var = (S2 - S1^2 / n) / (n - 1) comes out to ~1e-30 (mean^2 /
+//                          var + 1) relative -- R's two-pass var() to far below the 1e-12 the
+//                          tests ask; identical values give exactly 0, as two passes do.  Also
+//                          what the density needs (n, sum of good.reads, sd / min / max of
+//                          c(Bf, Af)).  At most 49 bytes per row: HBM-bound.
 //                          The het rows' (Bf, Af, good.reads) are copied next to each other
 //                          into the workspace (any order: everything downstream is
 //                          order-independent), so the density kernel streams 24 bytes per het
@@ -67,6 +69,16 @@ __device__ __forceinline__ D2 d2_add(D2 a, double x) {  // a + x, x finite
   return D2{h, lo - (h - s)};
 }
 __device__ __forceinline__ D2 d2_merge(D2 a, D2 b) { return d2_add(d2_add(a, b.hi), b.lo); }
+__device__ __forceinline__ D2 d2_sq(D2 a) {  // a^2
+  const double p = a.hi * a.hi;
+  const double e = fma(a.hi, a.hi, -p) + 2.0 * (a.hi * a.lo);
+  const double h = p + e;
+  return D2{h, e - (h - p)};
+}
+__device__ __forceinline__ D2 d2_add_sq(D2 acc, double x) {  // acc + x^2
+  const double p = x * x;
+  return d2_add(d2_add(acc, p), fma(x, x, -p));
+}
 __device__ __forceinline__ D2 d2_div(D2 a, double n) {  // a / n
   const double q = a.hi / n;
   const double r = fma(-q, n, a.hi) + a.lo;
@@ -137,7 +149,7 @@ __global__ void __launch_bounds__(kSegThreads)
 segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ cx,
                       double* __restrict__ cg, double* __restrict__ out) {
   __shared__ unsigned s_slot;
-  __shared__ D2 red[8 * 8];
+  __shared__ D2 red[9 * 8];
   __shared__ long long redl[8];
   __shared__ double redd[8];
   __shared__ int64_t s_lo, s_hi;
@@ -156,12 +168,20 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
   const bool W = a.weighted != 0;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
-  // pass 1: counts and sums
-  D2 sum[6] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};  // rw, w.r, v, vb, good, x
+  // one pass: counts, sums and sums of squares
+  D2 sum[9] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
+  // 0 rw, 1 w.r, 2 v, 3 v^2, 4 vb, 5 vb^2, 6 good, 7 x, 8 x^2
   long long nv = 0, nb = 0, nvb = 0, first = 0x7fffffffffffffffLL;
   double vmin = INF, vmax = -INF, bmin = INF, bmax = -INF, xmin = INF, xmax = -INF;
   for (int64_t i = lo + threadIdx.x; i < hi; i += kSegThreads) {
     const double r = a.ratio[i];
+    const double g = a.good[i];
+    const bool hb = a.het[i] && g >= a.min_reads;  // R/segments.R:128-129
+    double bf = 0., af = 0.;
+    if (hb) {
+      bf = a.Bf[i];
+      af = a.Af[i];
+    }
     double v;
     if (W) {
       const double wr = sqrt(a.dnorm[i]), rw = r * wr;  // R/segments.R:116-117
@@ -173,13 +193,12 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
     }
     if (!isnan(v)) {
       sum[2] = d2_add(sum[2], v);
+      sum[3] = d2_add_sq(sum[3], v);
       ++nv;
       vmin = fmin(vmin, v);
       vmax = fmax(vmax, v);
     }
-    const double g = a.good[i];
-    if (a.het[i] && g >= a.min_reads) {  // R/segments.R:128-129
-      const double bf = a.Bf[i], af = a.Af[i];
+    if (hb) {
       double vb = bf;
       if (W) {
         const double wb = sqrt(g);  // R/segments.R:118-119
@@ -188,20 +207,22 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       ++nb;
       if (i < first) first = i;
       if (!isnan(vb)) {
-        sum[3] = d2_add(sum[3], vb);
+        sum[4] = d2_add(sum[4], vb);
+        sum[5] = d2_add_sq(sum[5], vb);
         ++nvb;
         bmin = fmin(bmin, vb);
         bmax = fmax(bmax, vb);
       }
-      sum[4] = d2_add(sum[4], g);
-      sum[5] = d2_add(d2_add(sum[5], bf), af);
+      sum[6] = d2_add(sum[6], g);
+      sum[7] = d2_add(d2_add(sum[7], bf), af);
+      sum[8] = d2_add_sq(d2_add_sq(sum[8], bf), af);
+      xmin = fmin(xmin, fmin(bf, af));
+      xmax = fmax(xmax, fmax(bf, af));
       // compact copy for the density kernel: the segment owns cx[2 lo, 2 hi) and cg[lo, hi)
       const unsigned slot = atomicAdd(&s_slot, 1u);
       cx[2 * (lo + slot)] = bf;
       cx[2 * (lo + slot) + 1] = af;
       cg[lo + slot] = g;
-      xmin = fmin(xmin, fmin(bf, af));
-      xmax = fmax(xmax, fmax(bf, af));
     }
   }
   block_sum_d2(sum, red);
@@ -223,61 +244,33 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
     for (int w = 1; w < kSegThreads / 32; ++w) first = min(first, redl[w]);
     __syncthreads();
   }
-  const D2 mv = nv > 0 ? d2_div(sum[2], (double)nv) : D2{0, 0};
-  const D2 mb = nvb > 0 ? d2_div(sum[3], (double)nvb) : D2{0, 0};
-  const D2 mx = nb > 0 ? d2_div(sum[5], (double)(2 * nb)) : D2{0, 0};
-
-  // pass 2: squared deviations about the means (stats::var is two-pass)
-  D2 ss[3] = {{0, 0}, {0, 0}, {0, 0}};
-  auto dev2 = [](D2& acc, double x, const D2& m) {
-    const double d = (x - m.hi) - m.lo;
-    const double p = d * d;
-    acc = d2_add(d2_add(acc, p), fma(d, d, -p));
-  };
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kSegThreads) {
-    const double r = a.ratio[i];
-    double v = r;
-    if (W) {
-      const double wr = sqrt(a.dnorm[i]);
-      v = (r * wr) / wr;
-    }
-    if (!isnan(v)) dev2(ss[0], v, mv);
-    const double g = a.good[i];
-    if (a.het[i] && g >= a.min_reads) {
-      const double bf = a.Bf[i], af = a.Af[i];
-      double vb = bf;
-      if (W) {
-        const double wb = sqrt(g);
-        vb = (bf * wb) / wb;
-      }
-      if (!isnan(vb)) dev2(ss[1], vb, mb);
-      dev2(ss[2], bf, mx);
-      dev2(ss[2], af, mx);
-    }
-  }
-  block_sum_d2(ss, red);
   if (threadIdx.x != 0) return;
-  auto sd = [](const D2& q, long long n, double mn, double mxv) {
+  // stats::sd = sqrt(var), n - 1 in the denominator, NA below two values
+  auto sd = [](const D2& s1, const D2& s2, long long n, double mn, double mxv) {
     if (n < 2) return na_real();
     if (mn == mxv) return 0.0;  // identical values: exactly zero, as the two-pass var gives
-    return sqrt((q.hi + q.lo) / (double)(n - 1));
+    const D2 q = d2_div(d2_sq(s1), (double)n);
+    const D2 r = d2_add(d2_add(s2, -q.hi), -q.lo);
+    const double var = (r.hi + r.lo) / (double)(n - 1);
+    return sqrt(var > 0 ? var : 0.0);
   };
+  const D2 mv = nv > 0 ? d2_div(sum[2], (double)nv) : D2{0, 0};
   const int64_t S = a.S;
   double bfo = na_real();
   if (nb == 1) bfo = a.Bf[first];  // length(Bf) == 1 (R/model.R:93-94)
   out[0 * S + s] = bfo;            // nb >= 2: the density kernel fills it in
   out[1 * S + s] = (double)nb;
-  out[2 * S + s] = sd(ss[1], nvb, bmin, bmax);
+  out[2 * S + s] = sd(sum[4], sum[5], nvb, bmin, bmax);
   out[3 * S + s] = W ? (sum[0].hi + sum[0].lo) / (sum[1].hi + sum[1].lo)
                      : (nv > 0 ? mv.hi + mv.lo : __longlong_as_double(0x7FF8000000000000LL));
   out[4 * S + s] = (double)(hi - lo);
-  out[5 * S + s] = sd(ss[0], nv, vmin, vmax);
+  out[5 * S + s] = sd(sum[2], sum[3], nv, vmin, vmax);
   SegMid m;
   m.lo = lo;
   m.hi = hi;
   m.nb = nb;
-  m.gsum = sum[4].hi + sum[4].lo;
-  m.sdx = nb >= 1 ? sd(ss[2], 2 * nb, xmin, xmax) : 0.0;
+  m.gsum = sum[6].hi + sum[6].lo;
+  m.sdx = nb >= 1 ? sd(sum[7], sum[8], 2 * nb, xmin, xmax) : 0.0;
   m.xmin = xmin;
   m.xmax = xmax;
   m.x0 = nb >= 1 ? a.Bf[first] : 0.0;

@@ -65,7 +65,8 @@ def test_segment_stats_edge_cases(oracle):
     assert np.isnan(got[0, 0]) and got[0, 1] == 0
     assert got[1, 0] == g["Bf"][seg_rows[1][3]] and np.isnan(got[1, 2])
     assert got[2, 2] == 0.0 and got[2, 1] == 2
-    assert np.isnan(got[4, 3]) and np.isnan(got[4, 5]) and got[4, 4] == seg_rows[4].size
+    # all ratios NA: sum(rw, na.rm) / sum(w.r, na.rm) = 0 / positive, sd of nothing is NA
+    assert got[4, 3] == 0.0 and np.isnan(got[4, 5]) and got[4, 4] == seg_rows[4].size
     # cut(): a row AT a segment's start is outside it, one AT its end inside
     k = 2
     assert pos[seg_rows[k][-1]] <= brk[2 * k + 1] and (pos == brk[2 * k]).any()
