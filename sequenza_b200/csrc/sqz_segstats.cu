@@ -133,12 +133,24 @@ __device__ __forceinline__ double block_minmax(double v, bool is_max, double* re
   return t;
 }
 
-// first index in [a, b) whose position is > x (positions sorted)
-__device__ __forceinline__ int64_t upper_bound(const double* p, int64_t a, int64_t b, double x) {
-  while (a < b) {
-    const int64_t m = a + ((b - a) >> 1);
-    if (p[m] > x) b = m;
-    else a = m + 1;
+// first index in [a, b) whose position is > x (positions sorted; b if none), by the whole
+// CTA: every round samples the range at kSegThreads points, so a chromosome of a million rows
+// takes three dependent loads instead of twenty
+__device__ __forceinline__ int64_t block_upper_bound(const double* p, int64_t a, int64_t b,
+                                                     double x, int* sh) {
+  while (b > a) {  // block-uniform
+    const int64_t step = (b - a + kSegThreads - 1) / kSegThreads;
+    const int64_t idx = a + (int64_t)threadIdx.x * step;
+    if (threadIdx.x == 0) *sh = kSegThreads;
+    __syncthreads();
+    if (idx >= b || p[idx] > x) atomicMin(sh, (int)threadIdx.x);
+    __syncthreads();
+    const int first = *sh;  // first sample beyond x (or beyond the range)
+    __syncthreads();
+    const int64_t na = first > 0 ? a + (int64_t)(first - 1) * step + 1 : a;
+    const int64_t nb = first < kSegThreads ? (a + (int64_t)first * step < b ? a + (int64_t)first * step : b) : b;
+    a = na;
+    b = nb;
   }
   return a;
 }
@@ -152,19 +164,16 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
   __shared__ D2 red[9 * 8];
   __shared__ long long redl[8];
   __shared__ double redd[8];
-  __shared__ int64_t s_lo, s_hi;
+  __shared__ int s_first;
   const int64_t s = blockIdx.x;
-  if (threadIdx.x == 0) {
-    int64_t c = 0;
-    while (c + 1 < a.n_chr && a.seg_off[c + 1] <= s) ++c;
-    const int64_t r0 = a.row_off[c], r1 = a.row_off[c + 1];
-    // cut(position, breaks.vect): right-closed intervals (b0, b1] (R/segments.R:140-141)
-    s_lo = upper_bound(a.pos, r0, r1, a.brk[2 * s]);
-    s_hi = upper_bound(a.pos, s_lo, r1, a.brk[2 * s + 1]);
-    s_slot = 0;
-  }
+  int64_t c = 0;
+  while (c + 1 < a.n_chr && a.seg_off[c + 1] <= s) ++c;
+  const int64_t r0 = a.row_off[c], r1 = a.row_off[c + 1];
+  if (threadIdx.x == 0) s_slot = 0;
+  // cut(position, breaks.vect): right-closed intervals (b0, b1] (R/segments.R:140-141)
+  const int64_t lo = block_upper_bound(a.pos, r0, r1, a.brk[2 * s], &s_first);
+  const int64_t hi = block_upper_bound(a.pos, lo, r1, a.brk[2 * s + 1], &s_first);
   __syncthreads();
-  const int64_t lo = s_lo, hi = s_hi;
   const bool W = a.weighted != 0;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
 
