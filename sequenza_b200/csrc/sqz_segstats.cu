@@ -68,6 +68,19 @@ __device__ __forceinline__ D2 d2_add(D2 a, double x) {  // a + x, x finite
   const double h = s + lo;
   return D2{h, lo - (h - s)};
 }
+// streaming form: the high word takes the value, the rounding error of that one addition
+// goes to the low word (two-sum), no renormalisation -- the chain from row to row is a
+// single addition per accumulator; d2_merge at the end brings the pair back to normal form
+__device__ __forceinline__ void d2_acc(D2& a, double x) {
+  const double s = a.hi + x, bb = s - a.hi;
+  a.lo += (a.hi - (s - bb)) + (x - bb);
+  a.hi = s;
+}
+__device__ __forceinline__ void d2_acc_sq(D2& a, double x) {  // a += x^2
+  const double p = x * x;
+  d2_acc(a, p);
+  a.lo += fma(x, x, -p);
+}
 __device__ __forceinline__ D2 d2_merge(D2 a, D2 b) { return d2_add(d2_add(a, b.hi), b.lo); }
 __device__ __forceinline__ D2 d2_sq(D2 a) {  // a^2
   const double p = a.hi * a.hi;
@@ -194,15 +207,15 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
     double v;
     if (W) {
       const double wr = sqrt(a.dnorm[i]), rw = r * wr;  // R/segments.R:116-117
-      if (!isnan(rw)) sum[0] = d2_add(sum[0], rw);
-      if (!isnan(wr)) sum[1] = d2_add(sum[1], wr);
+      if (!isnan(rw)) d2_acc(sum[0], rw);
+      if (!isnan(wr)) d2_acc(sum[1], wr);
       v = rw / wr;
     } else {
       v = r;
     }
     if (!isnan(v)) {
-      sum[2] = d2_add(sum[2], v);
-      sum[3] = d2_add_sq(sum[3], v);
+      d2_acc(sum[2], v);
+      d2_acc_sq(sum[3], v);
       ++nv;
       vmin = fmin(vmin, v);
       vmax = fmax(vmax, v);
@@ -216,15 +229,17 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       ++nb;
       if (i < first) first = i;
       if (!isnan(vb)) {
-        sum[4] = d2_add(sum[4], vb);
-        sum[5] = d2_add_sq(sum[5], vb);
+        d2_acc(sum[4], vb);
+        d2_acc_sq(sum[5], vb);
         ++nvb;
         bmin = fmin(bmin, vb);
         bmax = fmax(bmax, vb);
       }
-      sum[6] = d2_add(sum[6], g);
-      sum[7] = d2_add(d2_add(sum[7], bf), af);
-      sum[8] = d2_add_sq(d2_add_sq(sum[8], bf), af);
+      d2_acc(sum[6], g);
+      d2_acc(sum[7], bf);
+      d2_acc(sum[7], af);
+      d2_acc_sq(sum[8], bf);
+      d2_acc_sq(sum[8], af);
       xmin = fmin(xmin, fmin(bf, af));
       xmax = fmax(xmax, fmax(bf, af));
       // compact copy for the density kernel: the segment owns cx[2 lo, 2 hi) and cg[lo, hi)
@@ -234,6 +249,8 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       cg[lo + slot] = g;
     }
   }
+#pragma unroll
+  for (int k = 0; k < 9; ++k) sum[k] = d2_add(D2{sum[k].hi, 0.}, sum[k].lo);  // normal form
   block_sum_d2(sum, red);
   nv = block_sum_ll(nv, redl);
   nb = block_sum_ll(nb, redl);
