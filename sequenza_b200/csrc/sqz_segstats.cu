@@ -88,10 +88,6 @@ __device__ __forceinline__ D2 d2_sq(D2 a) {  // a^2
   const double h = p + e;
   return D2{h, e - (h - p)};
 }
-__device__ __forceinline__ D2 d2_add_sq(D2 acc, double x) {  // acc + x^2
-  const double p = x * x;
-  return d2_add(d2_add(acc, p), fma(x, x, -p));
-}
 __device__ __forceinline__ D2 d2_div(D2 a, double n) {  // a / n
   const double q = a.hi / n;
   const double r = fma(-q, n, a.hi) + a.lo;
@@ -170,7 +166,7 @@ __device__ __forceinline__ int64_t block_upper_bound(const double* p, int64_t a,
 }  // namespace
 
 // ---- reductions of one segment (R/segments.R:140-170) -----------------------------------
-__global__ void __launch_bounds__(kSegThreads)
+__global__ void __launch_bounds__(kSegThreads, 2)
 segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ cx,
                       double* __restrict__ cg, double* __restrict__ out) {
   __shared__ unsigned s_slot;
@@ -195,18 +191,12 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
   // 0 rw, 1 w.r, 2 v, 3 v^2, 4 vb, 5 vb^2, 6 good, 7 x, 8 x^2
   long long nv = 0, nb = 0, nvb = 0, first = 0x7fffffffffffffffLL;
   double vmin = INF, vmax = -INF, bmin = INF, bmax = -INF, xmin = INF, xmax = -INF;
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kSegThreads) {
-    const double r = a.ratio[i];
-    const double g = a.good[i];
-    const bool hb = a.het[i] && g >= a.min_reads;  // R/segments.R:128-129
-    double bf = 0., af = 0.;
-    if (hb) {
-      bf = a.Bf[i];
-      af = a.Af[i];
-    }
+  auto row = [&](int64_t i, double r, double dn, double g, unsigned char het, double bf,
+                 double af) {
+    const bool hb = het && g >= a.min_reads;  // R/segments.R:128-129
     double v;
     if (W) {
-      const double wr = sqrt(a.dnorm[i]), rw = r * wr;  // R/segments.R:116-117
+      const double wr = sqrt(dn), rw = r * wr;  // R/segments.R:116-117
       if (!isnan(rw)) d2_acc(sum[0], rw);
       if (!isnan(wr)) d2_acc(sum[1], wr);
       v = rw / wr;
@@ -248,7 +238,30 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       cx[2 * (lo + slot) + 1] = af;
       cg[lo + slot] = g;
     }
+  };
+  // four rows per thread in flight: the loads of a batch are issued before any of it is
+  // consumed (the kernel is bound by memory latency, not by bandwidth or arithmetic)
+  constexpr int kBatch = 4;
+  int64_t i = lo + threadIdx.x;
+  for (; i + (kBatch - 1) * (int64_t)kSegThreads < hi; i += kBatch * (int64_t)kSegThreads) {
+    double r[kBatch], dn[kBatch], g[kBatch], bf[kBatch], af[kBatch];
+    unsigned char het[kBatch];
+#pragma unroll
+    for (int k = 0; k < kBatch; ++k) {
+      const int64_t ii = i + k * (int64_t)kSegThreads;
+      r[k] = a.ratio[ii];
+      dn[k] = W ? a.dnorm[ii] : 0.;
+      g[k] = a.good[ii];
+      het[k] = a.het[ii];
+      bf[k] = a.Bf[ii];
+      af[k] = a.Af[ii];
+    }
+#pragma unroll
+    for (int k = 0; k < kBatch; ++k)
+      row(i + k * (int64_t)kSegThreads, r[k], dn[k], g[k], het[k], bf[k], af[k]);
   }
+  for (; i < hi; i += kSegThreads)
+    row(i, a.ratio[i], W ? a.dnorm[i] : 0., a.good[i], a.het[i], a.Bf[i], a.Af[i]);
 #pragma unroll
   for (int k = 0; k < 9; ++k) sum[k] = d2_add(D2{sum[k].hi, 0.}, sum[k].lo);  // normal form
   block_sum_d2(sum, red);
