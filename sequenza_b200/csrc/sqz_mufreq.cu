@@ -397,6 +397,72 @@ mufreq_lookup_kernel(int64_t N, const double* __restrict__ F, const double* __re
   }
 }
 
+// The same lookup with 128-bit accesses: a thread takes two neighbouring positions (one
+// double2 load per input vector, one double2 store per output column) and two such pairs per
+// iteration; inputs and outputs are touched once, so they are loaded / stored with the
+// streaming hints and leave the L2 to the 326 KB answer table.  Needs an even N and 16-byte
+// aligned vectors (the launcher checks); positions outside the table take the direct
+// evaluation, as above.
+__global__ void __launch_bounds__(256)
+mufreq_lookup2_kernel(int64_t N, const double2* __restrict__ F2, const double2* __restrict__ R2,
+                      int nr, int nm, double wr, double wm, double cell, double ploidy,
+                      double adr, CnModel m, const double4* __restrict__ table,
+                      double* __restrict__ out) {
+  extern __shared__ double sm[];
+  double* probr = sm;
+  double* mm = sm + m.nc;
+  build_muf_model(m, cell, ploidy, adr, probr, mm);  // for the rare direct path
+  __syncthreads();
+  constexpr int U = 2;  // pairs per thread and iteration: four positions in flight
+  const int64_t NP = N >> 1, stride = (int64_t)gridDim.x * blockDim.x;
+  double2* o0 = reinterpret_cast<double2*>(out);
+  double2* o1 = reinterpret_cast<double2*>(out + N);
+  double2* o2 = reinterpret_cast<double2*>(out + 2 * N);
+  double2* o3 = reinterpret_cast<double2*>(out + 3 * N);
+  for (int64_t p0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p0 < NP; p0 += U * stride) {
+    double2 r[U], f[U];
+    double4 v[2 * U];
+    double kr[2 * U], km[2 * U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t p = p0 + u * stride;
+      r[u] = p < NP ? __ldcs(R2 + p) : make_double2(1.0, 1.0);
+      f[u] = p < NP ? __ldcs(F2 + p) : make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int u = 0; u < 2 * U; ++u) {
+      const double rr = (u & 1) ? r[u >> 1].y : r[u >> 1].x;
+      const double ff = (u & 1) ? f[u >> 1].y : f[u >> 1].x;
+      kr[u] = nearbyint(wr * (rr / (1 + rr)));  // R/bayes.R:26
+      km[u] = nearbyint(ff * wm);               // R/bayes.R:4
+      const bool in = kr[u] >= 0.0 && kr[u] < (double)nr && km[u] >= 0.0 && km[u] < (double)nm;
+      v[u] = table[in ? (int64_t)kr[u] * nm + (int64_t)km[u] : 0];
+    }
+#pragma unroll
+    for (int u = 0; u < 2 * U; ++u) {
+      const bool in = kr[u] >= 0.0 && kr[u] < (double)nr && km[u] >= 0.0 && km[u] < (double)nm;
+      if (!in && p0 + (u >> 1) * stride < NP) {  // NA, ratio < 0, F outside [0, 1]
+        const BinomHoist hr = binom_hoist(kr[u], wr), hm = binom_hoist(km[u], wm);
+        int kc, kt;
+        double lpp;
+        mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
+        v[u] = make_double4(kc >= 0 ? (double)m.CNn : na_real(),
+                            kc >= 0 ? (double)(m.CNt_min + kc) : na_real(),
+                            kc >= 0 ? (double)kt : na_real(), lpp);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t p = p0 + u * stride;
+      if (p >= NP) continue;
+      __stcs(o0 + p, make_double2(v[2 * u].x, v[2 * u + 1].x));
+      __stcs(o1 + p, make_double2(v[2 * u].y, v[2 * u + 1].y));
+      __stcs(o2 + p, make_double2(v[2 * u].z, v[2 * u + 1].z));
+      __stcs(o3 + p, make_double2(v[2 * u].w, v[2 * u + 1].w));
+    }
+  }
+}
+
 // number of table bytes sqz_mufreq_point_scalar_dev needs (0: weights not usable for the
 // table, the caller should use the vector-weight entry point)
 size_t mufreq_scalar_table_bytes(double wm, double wr) {
@@ -438,11 +504,18 @@ int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t
   if (tb > 148 * 16) tb = 148 * 16;
   mufreq_table_kernel<<<(unsigned)tb, 128, 0, st>>>(nr, nm, m, srp, smv, (double4*)table);
   SQZ_CUDA(cudaGetLastError());
-  int64_t blocks = (N + 255) / 256;
+  const bool vec2 = (N % 2 == 0) &&
+                    !(((uintptr_t)d_F | (uintptr_t)d_ratio | (uintptr_t)d_out) & 15);
+  int64_t blocks = ((vec2 ? N / 2 : N) + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
-  mufreq_lookup_kernel<<<(unsigned)blocks, 256, smb, st>>>(N, d_F, d_ratio, nr, nm, wr, wm,
-                                                          cellularity, ploidy, adr, m,
-                                                          (const double4*)table, d_out);
+  if (vec2)
+    mufreq_lookup2_kernel<<<(unsigned)blocks, 256, smb, st>>>(
+        N, (const double2*)d_F, (const double2*)d_ratio, nr, nm, wr, wm, cellularity, ploidy,
+        adr, m, (const double4*)table, d_out);
+  else
+    mufreq_lookup_kernel<<<(unsigned)blocks, 256, smb, st>>>(N, d_F, d_ratio, nr, nm, wr, wm,
+                                                            cellularity, ploidy, adr, m,
+                                                            (const double4*)table, d_out);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
 }
