@@ -111,6 +111,52 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
   }
 }
 
+// The same pre-pass for CNt 0..7 with two or more normal copies (what sequenza.fit always
+// runs, R/bayes.R:40): copy number c has c/2 + 1 BAF rows, 20 in all, known at compile time.
+// A lane keeps its column's 20 model BAFs and 8 prior weights in registers and the loops
+// unroll completely: ~300 instructions per segment and warp instead of ~2,600 (the generic
+// kernel walks the type table with run-time trip counts), which leaves the kernel bound by
+// the 8 bytes per (segment, copy number, column) it writes.  Same arithmetic, same bits:
+// scanning all rows finds the same nearest row as the bracket search above.
+__global__ void __launch_bounds__(256)
+baf_colterm_cg8_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_total,
+                       double* __restrict__ cwg) {
+  constexpr int NC = 8, T = 20;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int cg = blockIdx.y;
+  const int icl = min(cg * 32 + lane, nCb - 1);  // ragged last group repeats a column
+  const double cell = a.cell[ic0 + icl];
+  double mb[T], w[NC];
+  {
+    int t = 0;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      w[c] = m.w[c];
+#pragma unroll
+      for (int b = 0; b <= c / 2; ++b, ++t)
+        mb[t] = theoretical_baf((double)c, (double)b, cell, (double)m.CNn);  // R/model.R:9-14
+    }
+  }
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const int64_t sb = (int64_t)blockIdx.x * kPreSeg;
+  const int64_t se = min(sb + kPreSeg, N_total);
+  for (int64_t s = sb + warp; s < se; s += nwarp) {
+    const double2 bk = a.bk[s];
+    double* out = cwg + (((int64_t)cg * N_total + s) * NC) * 32 + lane;
+    int t = 0;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      double m0 = INF;  // min over B of |xb|: NaN never wins (R/bayes.R:70-72)
+#pragma unroll
+      for (int b = 0; b <= c / 2; ++b, ++t) {
+        const double x0 = fma(mb[t], bk.x, bk.y);
+        if (fabs(x0) < fabs(m0)) m0 = x0;
+      }
+      out[c * 32] = sqrt(fma(m0, m0, 1.0) * w[c]);
+    }
+  }
+}
+
 // ---- grid kernel -------------------------------------------------------------------------
 // What the analysis of one segment leaves for its evaluation, per lane, in shared memory:
 //   three doubles  k1, b1, w1: first candidate, x_j = fma(nld_j, k1, b1), q_j = fma(x_j, x_j, w1)
@@ -537,8 +583,11 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
     const int64_t ub = (u_end < g1 * a.nPT ? u_end : g1 * a.nPT) - g0 * a.nPT;
     if (nCb <= 0 || ub <= ua) continue;
     dim3 grid((unsigned)((N_total + kPreSeg - 1) / kPreSeg), (unsigned)((nCb + 31) / 32));
-    baf_colterm_cg_kernel<<<grid, 256, pre_smem, st>>>(a, m, (int)ic0, nCb, N_total,
-                                                       m.nc <= 8 ? 1 : 0, cwg);
+    if (m.nc == 8 && m.CNt_min == 0 && m.CNn >= 2 && m.T == 20)
+      baf_colterm_cg8_kernel<<<grid, 256, 0, st>>>(a, m, (int)ic0, nCb, N_total, cwg);
+    else
+      baf_colterm_cg_kernel<<<grid, 256, pre_smem, st>>>(a, m, (int)ic0, nCb, N_total,
+                                                         m.nc <= 8 ? 1 : 0, cwg);
     SQZ_CUDA(cudaGetLastError());
     int rc;
 #define SQZ_CW(PTV, NCV, SBV, OCCV)                                                       \
