@@ -18,9 +18,10 @@
 //             nothing is shared between them and the hardware scheduler balances them;
 //             the tiles of one (group, chunk) are neighbours in the grid and find each
 //             other's rows in L2.
-//   ring      two stages of 4 (CNt 0..7) or 1-2 (CNt 0..20) segments; lane 0 fills a stage with one TMA bulk copy
-//             (plus one for the segments' ratio terms) and completion is counted on an
-//             mbarrier; the stage is refilled as soon as the warp has left it.
+//   ring      two stages of 4 (CNt 0..7) or 1 (CNt 0..20) segments; lane 0 fills a stage
+//             with one TMA bulk copy (plus one or two for the segments' ratio terms) and
+//             completion is counted on an mbarrier; the stage is refilled as soon as the
+//             warp has left it.
 //   batch     the segments of a stage are analysed together (bounds, argmin, dynamic loads,
 //             warp vote: a serial chain per segment, independent between segments; results
 //             parked in shared memory), then evaluated one after the other by ONE copy of
@@ -164,8 +165,13 @@ baf_colterm_cg8_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tot
 //                  (a lane without a further one repeats its first)
 //   word 1         upper bound of the binary exponent the products gain | (the longest
 //                  candidate list in the warp, warp-uniform) << 16
+// (the two words share an 8-byte slot next to the doubles: a record is [4][32] doubles)
 
-template <int PT, int NC, int SB, int OCC>
+// (Measured and dropped: two warps sharing a CTA's tile, 16 ploidies and half of a stage's
+// analyses each, handed over in shared memory -- 128 registers, four warps per scheduler:
+// 31.4 ms on config 3 against 31.3 for one warp; with three per scheduler at 168 registers
+// the same.  More warps do not help: the kernel is bound by issue, not by latency.)
+template <int PT, int NC, int SB, int OCC, bool F32>
 __global__ void __launch_bounds__(32, OCC)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
                         int nCb, int ub0, int nUb, int64_t N_total, double* __restrict__ partM,
@@ -179,10 +185,11 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const int lane = threadIdx.x, tid = threadIdx.x;
   double* stage = sm;                                                           // [kRing][kSegB][NC][32]
   double2* rkS = reinterpret_cast<double2*>(stage + kRing * kSegB * kSegDoubles);  // [kRing][kSegB]
-  double* lm = reinterpret_cast<double*>(rkS + kRing * kSegB) + lane;          // [NC][32]
-  int* Ec = reinterpret_cast<int*>(lm - lane + NC * 32);                        // [PT][32]
-  double* pk = reinterpret_cast<double*>(Ec + PT * 32) + lane;                  // [kSegB][3][32]
-  unsigned* pw = reinterpret_cast<unsigned*>(pk - lane + kSegB * 3 * 32) + lane;  // [kSegB][2][32]
+  float4* rfS = reinterpret_cast<float4*>(rkS + kRing * kSegB);                 // [kRing][kSegB]
+  double* lm = reinterpret_cast<double*>(rfS + kRing * kSegB) + lane;          // [NC][32]
+  float* lmf = reinterpret_cast<float*>(lm - lane + NC * 32) + lane;            // [NC][32] (F32)
+  int* Ec = reinterpret_cast<int*>(lmf - lane + (F32 ? NC * 32 : 0));           // [PT][32]
+  double* pk = reinterpret_cast<double*>(Ec + PT * 32) + lane;                  // [kSegB][4][32]
   __shared__ __align__(8) unsigned long long full[kRing];
 
   // CTA -> (unit of this launch, chunk, sample); units run tile-fastest inside a column
@@ -221,14 +228,32 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   const double nmid = 0.5 * (nld[0] + nld[PT - 1]);
 #pragma unroll
   for (int j = 0; j < PT; ++j) nld[j] -= nmid;
-  const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
 #pragma unroll 1
   for (int c = 0; c < NC; ++c) {
     const double A = (1 - cell) + ((double)(m.CNt_min + c) / (double)m.CNn * cell);
-    lm[c * 32] = log(adr * A) + nmid;
+    const double l = log(adr * A) + nmid;
+    lm[c * 32] = l;
+    if (F32) lmf[c * 32] = __double2float_rn(l);
   }
 #pragma unroll
   for (int j = 0; j < PT; ++j) Ec[j * nthr + tid] = 0;
+  // The bounds of the analysis are taken in fp32, rounded so that they never exceed the
+  // fp64 value (see analyse).  hcf: half-width of the tile in -log D plus the rounding the
+  // fp32 midpoint residual can carry, per unit of |k|: 2^-22 (|lm| + half-width) covers the
+  // conversions of lm, k, b and the fused multiply-add (2^-24 each) with room to spare; the
+  // part that scales with |b| comes with the segment (rk32.z).
+  const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
+  float hcf = 0.f;
+  if (F32) {
+    float lmax = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < NC; ++c) {
+      const float v = fabsf(lmf[c * 32]);
+      // (-Inf, cellularity 1 with CNt 0, gives an infinite residual whatever the margin)
+      if (v < __int_as_float(0x7F800000)) lmax = fmaxf(lmax, v);
+    }
+    hcf = __double2float_ru(hw * (1.0 + 0x1p-22) + 0x1p-22 * (double)lmax);
+  }
 
   const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
   const int64_t per = (s1 - s0 + a.nChunk - 1) / a.nChunk;
@@ -241,19 +266,23 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // __syncwarp before the call).
   const double* f_src = cwc + cb * kSegDoubles;
   const double2* f_rk = a.rk + cb;
+  const float4* f_rf = a.rk32 + cb;
   int64_t f_left = ce - cb;  // segments not yet requested
   int f_s = 0;
   auto fetch = [&]() {
     if (f_left <= 0) return;
     const unsigned cnt = f_left < kSegB ? (unsigned)f_left : (unsigned)kSegB;
     if (lane == 0) {
-      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2)));
+      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2) +
+                                                  (F32 ? sizeof(float4) : 0)));
       tma_bulk_g2s(stage + f_s * kSegB * kSegDoubles, f_src,
                    cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[f_s]);
       tma_bulk_g2s(rkS + f_s * kSegB, f_rk, cnt * (unsigned)sizeof(double2), &full[f_s]);
+      if (F32) tma_bulk_g2s(rfS + f_s * kSegB, f_rf, cnt * (unsigned)sizeof(float4), &full[f_s]);
     }
     f_src += kSegB * kSegDoubles;
     f_rk += kSegB;
+    f_rf += kSegB;
     f_left -= kSegB;
     f_s ^= 1;
   };
@@ -275,31 +304,70 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // independent chains overlap only if they are interleaved in the instruction stream.  The
   // warp votes and the stores come last: a warp-synchronous operation or a shared-memory
   // store in the middle would pin the order.
-  auto analyse = [&](int base, auto bt) {
+  // (base: the first segment's slot in the ring; slot0: its slot in the stage, where the
+  // results are parked)
+  auto analyse = [&](int base, int slot0, auto bt) {
     constexpr int B = decltype(bt)::value;
     double2 rk[B];
     const double* col[B];
     unsigned lbh[B][NC], kbest[B];
+    float kf[B], bf[B], sf[B];
 #pragma unroll
     for (int g = 0; g < B; ++g) {
       rk[g] = rkS[base + g];
+      if (F32) {
+        const float4 rf = rfS[base + g];
+        kf[g] = rf.x;
+        bf[g] = rf.y;
+        // what |x_mid| may lose: the half-width of the tile and the rounding
+        sf[g] = __fmaf_ru(fabsf(rf.x), hcf, rf.z);
+      }
       col[g] = stage + (base + g) * kSegDoubles + lane;  // stored value of c: [c * 32]
       kbest[g] = 0xFFFFFFFFu;
     }
-    // (a) lower bound of every copy number over the tile (high words are enough: Qmax
-    // below has a zero low word); argmin on the high words with the index packed in.
-    // max(t0, 0) = t0/2 + |t0/2| with exact halves: one DADD, no compare and selects.
+    // (a) lower bound of every copy number over the tile, wub (1 + t^2) with t = max(|x_mid|
+    // - half-width, 0); argmin with the copy number packed into the low bits.
+    if (F32) {
+      // CNt 0..7: in fp32 and never above the fp64 value.  The midpoint residual loses its
+      // rounding margin (sf), the stored factor is cut to the 20 mantissa bits of its high
+      // word (it is >= 1: the priors are normalised, R/bayes.R:59, so the exponent needs a
+      // cap only at the top), products and sums round down.  A bound that is a little low
+      // costs an evaluation, never a result.  Bit patterns of non-negative floats order as
+      // integers.
 #pragma unroll
-    for (int c = 0; c < NC; ++c) {
-      const double lmc = lm[c * 32];
+      for (int c = 0; c < NC; ++c) {
+        const float lmc = lmf[c * 32];
 #pragma unroll
-      for (int g = 0; g < B; ++g) {
-        const double hx = 0.5 * rk[g].x, hy = 0.5 * rk[g].y;
-        const double t0 = fabs(fma(lmc, hx, hy)) - hw * fabs(hx);
-        const double t = t0 + fabs(t0);
-        const double rv = col[g][c * 32], u = SQ ? rv * t : t * t;
-        lbh[g][c] = (unsigned)__double2hiint(SQ ? fma(u, u, rv * rv) : fma(rv, u, rv));
-        kbest[g] = min(kbest[g], (lbh[g][c] & 0xFFFFFFC0u) | (unsigned)c);
+        for (int g = 0; g < B; ++g) {
+          const float t = fmaxf(__fsub_rd(fabsf(fmaf(lmc, kf[g], bf[g])), sf[g]), 0.f);
+          const unsigned hi = reinterpret_cast<const unsigned*>(col[g])[c * 64 + 1];
+          const float rv = __uint_as_float(min(hi, 0x47EFFFFFu) * 8u + 0x40000000u);
+          float lb;
+          if (SQ) {
+            const float u = __fmul_rd(rv, t);
+            lb = __fmaf_rd(u, u, __fmul_rd(rv, rv));
+          } else {
+            lb = __fmul_rd(rv, __fmaf_rd(t, t, 1.f));
+          }
+          lbh[g][c] = __float_as_uint(lb);
+          kbest[g] = min(kbest[g], (lbh[g][c] & 0xFFFFFFC0u) | (unsigned)c);
+        }
+      }
+    } else {
+      // CNt 0..20: in fp64, compared on the high words (the float copy of lm would cost two
+      // of the twelve warps per SM).  max(t0, 0) = t0/2 + |t0/2| with exact halves: one DADD.
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        const double lmc = lm[c * 32];
+#pragma unroll
+        for (int g = 0; g < B; ++g) {
+          const double hx = 0.5 * rk[g].x, hy = 0.5 * rk[g].y;
+          const double t0 = fabs(fma(lmc, hx, hy)) - hw * fabs(hx);
+          const double t = t0 + fabs(t0);
+          const double rv = col[g][c * 32], u = SQ ? rv * t : t * t;
+          lbh[g][c] = (unsigned)__double2hiint(SQ ? fma(u, u, rv * rv) : fma(rv, u, rv));
+          kbest[g] = min(kbest[g], (lbh[g][c] & 0xFFFFFFC0u) | (unsigned)c);
+        }
       }
     }
     // (b) the most promising copy number
@@ -327,16 +395,19 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
       qh[g] = max((unsigned)__double2hiint(fma(xa, xa, w1[g])) & 0x7FFFFFFFu,
                   (unsigned)__double2hiint(fma(xb, xb, w1[g])) & 0x7FFFFFFFu);
     }
-    // (d) copy numbers that can still lower a minimum: lb < Qmax = (qh + 1, 0), i.e. the
-    // high word of lb is at most qh; Qmax = +Inf keeps every finite bound
+    // (d) copy numbers that can still lower a minimum: bound < Qmax, the double (qh + 1, 0),
+    // which is exact as a float (20 mantissa bits; beyond the float range: +Inf, which
+    // keeps every finite bound)
     unsigned need[B];
 #pragma unroll
     for (int g = 0; g < B; ++g) {
-      const unsigned qcap = qh[g] >= 0x7FF00000u ? 0x7FEFFFFFu : qh[g];
+      // (fp64 bounds: high word of the bound at most qh; Qmax = +Inf keeps every finite one)
+      const unsigned qcap = F32 ? min(qh[g] + 1u, 0x47F00000u) * 8u + 0x40000000u
+                                : (qh[g] >= 0x7FF00000u ? 0x7FF00000u : qh[g] + 1u);
       need[g] = 0;
 #pragma unroll
       for (int c = 0; c < NC; ++c)
-        if (lbh[g][c] <= qcap) need[g] |= 1u << c;
+        if (lbh[g][c] < qcap) need[g] |= 1u << c;
       need[g] &= ~(1u << first[g]);
     }
     unsigned nmax[B];
@@ -344,11 +415,13 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     for (int g = 0; g < B; ++g) nmax[g] = __reduce_max_sync(0xffffffffu, (unsigned)__popc(need[g]));
 #pragma unroll
     for (int g = 0; g < B; ++g) {
-      pk[(g * 3 + 0) * 32] = k1[g];
-      pk[(g * 3 + 1) * 32] = b1[g];
-      pk[(g * 3 + 2) * 32] = w1[g];
-      pw[(g * 2 + 0) * 32] = need[g] | ((unsigned)first[g] << 24);
-      pw[(g * 2 + 1) * 32] = (qh[g] >> 20) | (nmax[g] << 16);  // exponent field: at most 0x7FF
+      double* pr = pk + (slot0 + g) * 4 * 32;
+      pr[0 * 32] = k1[g];
+      pr[1 * 32] = b1[g];
+      pr[2 * 32] = w1[g];
+      *reinterpret_cast<uint2*>(pr + 3 * 32) =
+          make_uint2(need[g] | ((unsigned)first[g] << 24),
+                     (qh[g] >> 20) | (nmax[g] << 16));  // exponent field: at most 0x7FF
     }
   };
 
@@ -358,16 +431,16 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     unsigned need, nmax;
     int first, gr;
   };
-  auto load_par = [&](int idx) {
+  auto load_par = [&](const double* pr) {
     CwPar sg;
-    sg.k1 = pk[(idx * 3 + 0) * 32];
-    sg.b1 = pk[(idx * 3 + 1) * 32];
-    sg.w1 = pk[(idx * 3 + 2) * 32];
-    const unsigned w0 = pw[(idx * 2 + 0) * 32], w1 = pw[(idx * 2 + 1) * 32];
-    sg.need = w0 & 0x00FFFFFFu;
-    sg.first = (int)(w0 >> 24);
-    sg.gr = (int)(w1 & 0xFFFFu) - 1021;
-    sg.nmax = w1 >> 16;
+    sg.k1 = pr[0 * 32];
+    sg.b1 = pr[1 * 32];
+    sg.w1 = pr[2 * 32];
+    const uint2 w = *reinterpret_cast<const uint2*>(pr + 3 * 32);
+    sg.need = w.x & 0x00FFFFFFu;
+    sg.first = (int)(w.x >> 24);
+    sg.gr = (int)(w.y & 0xFFFFu) - 1021;
+    sg.nmax = w.y >> 16;
     return sg;
   };
   auto evaluate = [&](int slot, const CwPar& sg) {
@@ -446,27 +519,22 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     const int base = s * kSegB;
     const int nsg = left < kSegB ? (int)left : kSegB;
     if (nsg == kSegB) {
-      analyse(base, std::integral_constant<int, kSegB>());
-    } else if (nsg >= 2 && kSegB > 2) {  // ragged last stage of the chunk
-      analyse(base, std::integral_constant<int, 2>());
-      if (nsg == 3) {
-        // the third segment's results go to slot 2: shift the parking position
-        pk += 2 * 3 * 32;
-        pw += 2 * 2 * 32;
-        analyse(base + 2, std::integral_constant<int, 1>());
-        pk -= 2 * 3 * 32;
-        pw -= 2 * 2 * 32;
+      analyse(base, 0, std::integral_constant<int, kSegB>());
+    } else {  // ragged last stage of the chunk
+      int k = 0;
+      if (kSegB > 2 && nsg >= 2) {
+        analyse(base, 0, std::integral_constant<int, (kSegB > 2 ? 2 : 1)>());
+        k = 2;
       }
-    } else {
-      analyse(base, std::integral_constant<int, 1>());
+      if (nsg > k) analyse(base + k, k, std::integral_constant<int, 1>());
     }
     // (each lane reads back only what it wrote itself: no warp synchronisation needed);
     // the parameters of the next segment are loaded while the current one is evaluated
     {
-      CwPar cur = load_par(0);
+      CwPar cur = load_par(pk);
 #pragma unroll 1
       for (int sg = 0; sg < nsg; ++sg) {
-        const CwPar nxt = load_par(sg + 1 < nsg ? sg + 1 : sg);
+        const CwPar nxt = load_par(pk + (sg + 1 < nsg ? sg + 1 : sg) * 4 * 32);
         evaluate(base + sg, cur);
         cur = nxt;
       }
@@ -517,11 +585,13 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 }
 
 // ---- host side ---------------------------------------------------------------------------
-static size_t colwarp_smem_bytes(int NC, int PT, int segb) {
+static size_t colwarp_smem_bytes(int NC, int PT, int segb, bool f32) {
   const int ring = 2;
-  return (size_t)ring * segb * NC * 32 * sizeof(double) + ring * segb * sizeof(double2) +
-         (size_t)NC * 32 * sizeof(double) + (size_t)PT * 32 * sizeof(int) +
-         (size_t)segb * 32 * (3 * sizeof(double) + 2 * sizeof(unsigned));
+  return (size_t)ring * segb * NC * 32 * sizeof(double) +
+         ring * segb * (sizeof(double2) + sizeof(float4)) +
+         (size_t)NC * 32 * (sizeof(double) + (f32 ? sizeof(float) : 0)) +
+         (size_t)PT * 32 * sizeof(int) +
+         (size_t)segb * 32 * 4 * sizeof(double);
 }
 
 static size_t colterm_cg_smem_bytes(int nc, int T) {
@@ -541,18 +611,18 @@ size_t baf_colwarp_group_bytes(int nc, int64_t N_total) {
   return (size_t)nc * 32 * sizeof(double) * (size_t)(N_total > 0 ? N_total : 1);
 }
 
-template <int PT, int NC, int SB, int OCC>
+template <int PT, int NC, int SB, int OCC, bool F32>
 static int launch_colwarp(const BafGridArgs& a, const CnModel& m, int64_t N_total,
                           const double* cwg, int ic0, int nCb, int ub0, int nUb, double* partM,
                           long long* partE, unsigned long long* stats, cudaStream_t st) {
   const int64_t ctas = a.S * (int64_t)nUb * a.nChunk;
   if (ctas > 0x7fffffffLL) return fail(SQZ_ERR_SIZE, "grid too large for one launch");
-  const size_t smb = colwarp_smem_bytes(NC, PT, SB);
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC>,
+  const size_t smb = colwarp_smem_bytes(NC, PT, SB, F32);
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC, F32>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024));
-  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC>,
+  SQZ_CUDA(cudaFuncSetAttribute(baf_grid_colwarp_kernel<PT, NC, SB, OCC, F32>,
                                 cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-  baf_grid_colwarp_kernel<PT, NC, SB, OCC><<<(unsigned)ctas, 32, smb, st>>>(
+  baf_grid_colwarp_kernel<PT, NC, SB, OCC, F32><<<(unsigned)ctas, 32, smb, st>>>(
       a, m, cwg, ic0, nCb, ub0, nUb, N_total, partM, partE, stats);
   SQZ_CUDA(cudaGetLastError());
   return SQZ_OK;
@@ -590,9 +660,9 @@ int baf_colwarp_run(const BafGridArgs& a, const CnModel& m, int PT, int64_t N_to
                                                          m.nc <= 8 ? 1 : 0, cwg);
     SQZ_CUDA(cudaGetLastError());
     int rc;
-#define SQZ_CW(PTV, NCV, SBV, OCCV)                                                       \
-  rc = launch_colwarp<PTV, NCV, SBV, OCCV>(a, m, N_total, cwg, (int)ic0, nCb, (int)ua,    \
-                                           (int)(ub - ua), partM, partE, stats, st)
+#define SQZ_CW(PTV, NCV, SBV, OCCV)                                                     \
+  rc = launch_colwarp<PTV, NCV, SBV, OCCV, (NCV <= 8)>(                                 \
+      a, m, N_total, cwg, (int)ic0, nCb, (int)ua, (int)(ub - ua), partM, partE, stats, st)
     // (measured and dropped: two segments per stage, 36.4 ms against 34.4; twelve warps
     // per SM at 168 registers with two per stage, 51 ms -- the spills cost more than the
     // occupancy gains)

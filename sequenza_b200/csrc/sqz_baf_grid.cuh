@@ -24,6 +24,8 @@ struct BafGridArgs {
   const int64_t* seg_off;  // [S+1]
   const double *Bf, *ratio, *sdBf, *sdr, *wBf, *wr;  // raw per-segment vectors
   const double2* rk;  // fast path: (kr, er)   xr/sqrt5 = fma(log mr, kr, er)
+  // (kr, er) as floats and 2^-22 |er| rounded up: fp32 bounds of the column-per-lane kernel
+  const float4* rk32;
   const double2* bk;  // fast path: (kb, eb)   xb/sqrt5 = fma(mb, kb, eb)
   const int* nB;      // [S] segments that carry a BAF term
   const double* adr;  // [S] avg.depth.ratio
