@@ -277,21 +277,29 @@ def run_reference(args, rank, world):
 def roofline_model(w, plan, kpath, n_cand, ncall, cols, nP, n):
     """Executed work per evaluation of the kernel path that ran.
     Returns (candidates per (segment, tile), fp64-pipe instructions, math-dispatch slots,
-    flops) per evaluation.  Per evaluated (copy number, ploidy): 2 DFMA (+ DSETP and 2 FSEL
+    fp64 flops, fp32 flops) per evaluation.  Per evaluated (copy number, ploidy): 2 DFMA (+ DSETP and 2 FSEL
     from the second candidate on); per ploidy 1 DMUL into the running product; the
     per-column pre-pass is shared by all nP ploidies of a column."""
     PT, nPT = plan["PT"], plan["nPT"]
     n_c, T = w["n_c"], w["T"]
     pre = (2.0 * T + 14.0 * n_c) / nP
+    f32 = 0.0
     if kpath == 3 and ncall > 0:
-        # column-per-lane kernel: per (segment, tile) ~7 fp64 + 4 integer instructions per
-        # copy number for the bounds and ~10 + ~10 to set up the first candidate; the first
+        # column-per-lane kernel, per (segment, tile): the bounds (per copy number 7 fp64 + 4
+        # integer instructions for CNt 0..20; 6 fp32 + 6 integer ones, off the fp64 pipe, for
+        # CNt 0..7) and ~10 fp64 + ~10 others to set up the first candidate; the first
         # candidate costs 2 DFMA + DMUL per ploidy (no minimum), every further one that the
         # warp evaluates 2 DFMA + DSETP + 2 FSEL
         cand = n_cand / (float(ncall) * n * cols * nPT)
-        inst = 3.0 + (cand - 1.0) * 3.0 + (7.0 * n_c + 10.0) / PT + pre
-        math = inst + (cand - 1.0) * 2.0 + (4.0 * n_c + 10.0) / PT
-        flop = 5.0 + (cand - 1.0) * 5.0 + (9.0 * n_c + 14.0) / PT + 1.5 * pre
+        if n_c <= 8:
+            inst = 3.0 + (cand - 1.0) * 3.0 + 10.0 / PT + pre
+            math = inst + (cand - 1.0) * 2.0 + (12.0 * n_c + 10.0) / PT
+            flop = 5.0 + (cand - 1.0) * 5.0 + 14.0 / PT + 1.5 * pre
+            f32 = 8.0 * n_c / PT
+        else:
+            inst = 3.0 + (cand - 1.0) * 3.0 + (7.0 * n_c + 10.0) / PT + pre
+            math = inst + (cand - 1.0) * 2.0 + (4.0 * n_c + 10.0) / PT
+            flop = 5.0 + (cand - 1.0) * 5.0 + (9.0 * n_c + 14.0) / PT + 1.5 * pre
     elif kpath == 2 and ncall > 0:
         cand = n_cand / (float(ncall) * n * cols * nPT)
         inst = cand * (3.0 + 2.0 / PT) + 1 + 6.0 * n_c / PT + pre
@@ -302,7 +310,7 @@ def roofline_model(w, plan, kpath, n_cand, ncall, cols, nP, n):
         inst = 3.0 * n_c + 1 + 3.0 * n_c / PT + pre         # fp64-pipe issue slots
         math = inst + 2.0 * n_c                             # + the FSEL pair of each minimum
         flop = 5.0 * n_c + 1 + 3.0 * n_c / PT + 1.5 * pre   # DFMA = 2 flops, others 1
-    return cand, inst, math, flop
+    return cand, inst, math, flop, f32
 
 
 def measure_grid(w, env, steps, warmup, with_e2e=True):
@@ -476,7 +484,8 @@ def roofline_block(w, m, peak, world, local_rank):
     from sequenza_b200.dist import unit_points
     local_points = float(unit_points(plan, nC, nP, u0, u1).sum())
     cols = local_points / nP  # column equivalents
-    cand, inst, math, flop = roofline_model(w, plan, kpath, m["n_cand"], ncall, cols, nP, n)
+    cand, inst, math, flop, f32 = roofline_model(w, plan, kpath, m["n_cand"], ncall, cols, nP,
+                                                 n)
     fast_ms = m["ms3"][1] / max(ncall, 1)
     local_evals = local_points * n
     padded = float(nPT * PT) / nP  # ragged last ploidy tile is computed and discarded
@@ -496,6 +505,7 @@ def roofline_block(w, m, peak, world, local_rank):
         "kernel_ms": fast_ms,
         "kernel_share_of_step": fast_ms / m["ms_per_step"] if m["ms_per_step"] else None,
         "fp64_issue_slots_per_eval": inst, "flops_per_eval_executed": flop,
+        "fp32_flops_per_eval_executed": f32,
         "pipe_util": (local_evals * inst / (fast_ms * 1e-3)) / (peak * 1e12 / 2)
         if fast_ms > 0 and peak else None,
         "math_issue_slots_per_eval": math,
