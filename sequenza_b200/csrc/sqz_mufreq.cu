@@ -16,6 +16,8 @@
 //     they are evaluated once per position (and, for the grid, once per fit in a
 //     preparation pass) instead of once per row;
 //   - rows outside CN* never reach the output, so only the CN* rows get a score.m.
+#include <stdlib.h>
+
 #include "sqz_common.cuh"
 #include "../../include/sequenza_b200.h"
 
@@ -309,39 +311,68 @@ mufreq_scores_kernel(int nr, int nm, double wr, double wm, double cell, double p
 
 // Stage 2: which.max(score.r) per kr (first maximum, NaN skipped), then for every (kr, km)
 // the first maximum of log(post) among the rows of that copy number (R/bayes.R:155-164).
-__global__ void __launch_bounds__(128)
+// One WARP per pair of counts: the lanes take the copy numbers, then the rows, and a
+// shuffle reduction keeps the first maximum (a thread per pair walked up to 21 logarithms
+// one after the other: 15 us of latency for a 40 KB table).  Besides the double4 answers
+// (what the global-memory lookup reads) the table is written in a compact form, 8 bytes of
+// LPP and a 16-bit code (CNt << 8 | Mt, 0xFFFF = NA) per pair, which fits shared memory.
+struct FirstMax {
+  double v;
+  int k;  // -1: none yet
+};
+__device__ __forceinline__ FirstMax first_max(FirstMax a, FirstMax b) {
+  if (b.k < 0) return a;
+  if (a.k < 0) return b;
+  if (b.v > a.v || (b.v == a.v && b.k < a.k)) return b;
+  return a;
+}
+__device__ __forceinline__ FirstMax warp_first_max(FirstMax a) {
+#pragma unroll
+  for (int off = 16; off; off >>= 1) {
+    FirstMax b;
+    b.v = __shfl_xor_sync(0xffffffffu, a.v, off);
+    b.k = __shfl_xor_sync(0xffffffffu, a.k, off);
+    a = first_max(a, b);
+  }
+  return a;
+}
+
+constexpr unsigned kMufNaCode = 0xFFFFu;
+
+__global__ void __launch_bounds__(256)
 mufreq_table_kernel(int nr, int nm, CnModel m, const double* __restrict__ srp,
-                    const double* __restrict__ smv, double4* __restrict__ table) {
+                    const double* __restrict__ smv, double4* __restrict__ table,
+                    double* __restrict__ lpp8, unsigned short* __restrict__ code16) {
+  const int lane = threadIdx.x & 31;
   const int64_t n = (int64_t)nr * nm;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * blockDim.x) {
+  const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
     const int kr = (int)(i / nm), km = (int)(i - (int64_t)kr * nm);
-    int kc = -1;
-    double bests = 0.;
-    for (int c = 0; c < m.nc; ++c) {
+    FirstMax bc = {0., -1};
+    for (int c = lane; c < m.nc; c += 32) {
       const double sr = srp[(int64_t)kr * m.nc + c];
-      if (!isnan(sr) && (kc < 0 || sr > bests)) {
-        bests = sr;
-        kc = c;
-      }
+      if (!isnan(sr) && (bc.k < 0 || sr > bc.v)) bc = {sr, c};
     }
-    int k = -1;
-    double best = 0.;
+    bc = warp_first_max(bc);
+    const int kc = bc.k;
+    FirstMax bt = {0., -1};
     if (kc >= 0)
-      for (int t = m.toff[kc]; t < m.toff[kc + 1]; ++t) {
-        double post = bests * smv[(int64_t)km * m.T + t];
+      for (int t = m.toff[kc] + lane; t < m.toff[kc + 1]; t += 32) {
+        double post = bc.v * smv[(int64_t)km * m.T + t];
         if (post == 0) post = __longlong_as_double(2LL);  // 1e-323
         const double lp = log(post);
-        if (!isnan(lp) && (k < 0 || lp > best)) {
-          best = lp;
-          k = t;
-        }
+        if (!isnan(lp) && (bt.k < 0 || lp > bt.v)) bt = {lp, t};
       }
-    const bool ok = kc >= 0 && k >= 0;
-    table[i] = make_double4(ok ? (double)m.CNn : na_real(),
-                            ok ? (double)(m.CNt_min + kc) : na_real(),
-                            ok ? (double)(k - m.toff[kc]) : na_real(),
-                            ok ? best : __longlong_as_double(0x7FF8000000000000LL));
+    bt = warp_first_max(bt);
+    if (lane == 0) {
+      const bool ok = kc >= 0 && bt.k >= 0;
+      const int cnt = ok ? m.CNt_min + kc : 0, mt = ok ? bt.k - m.toff[kc] : 0;
+      const double lpp = ok ? bt.v : __longlong_as_double(0x7FF8000000000000LL);
+      table[i] = make_double4(ok ? (double)m.CNn : na_real(), ok ? (double)cnt : na_real(),
+                              ok ? (double)mt : na_real(), lpp);
+      lpp8[i] = lpp;
+      code16[i] = (unsigned short)(ok ? ((unsigned)cnt << 8 | (unsigned)mt) : kMufNaCode);
+    }
   }
 }
 
@@ -463,15 +494,130 @@ mufreq_lookup2_kernel(int64_t N, const double2* __restrict__ F2, const double2* 
   }
 }
 
+// The lookup with the compact table in SHARED memory (101 x 101 pairs: 100 KB, two CTAs per
+// SM): every position costs one 8-byte and one 2-byte shared-memory load instead of a
+// 32-byte gather through L1/L2, whose tag stage -- 32 different lines per warp request --
+// took as long as the HBM streams themselves.  Inputs and outputs as in
+// mufreq_lookup2_kernel (128-bit streaming accesses, two pairs of positions per thread and
+// iteration).  Copy numbers and row numbers come back as doubles by the 2^52 trick.
+__device__ __forceinline__ double small_uint_to_double(unsigned k) {
+  return __hiloint2double(0x43300000, (int)k) - 4503599627370496.0;
+}
+
+// positions outside the table (NA, ratio < 0, F outside [0, 1]): the direct evaluation, kept
+// out of line so that the streaming loop stays within 64 registers
+__device__ __noinline__ double4 muf_direct(const CnModel& m, const double* probr,
+                                           const double* mm, double kr, double wr, double km,
+                                           double wm) {
+  const BinomHoist hr = binom_hoist(kr, wr), hm = binom_hoist(km, wm);
+  int kc, kt;
+  double lpp;
+  mufreq_eval(m, probr, mm, hr, hm, kc, kt, lpp);
+  return make_double4(kc >= 0 ? (double)m.CNn : na_real(),
+                      kc >= 0 ? (double)(m.CNt_min + kc) : na_real(),
+                      kc >= 0 ? (double)kt : na_real(), lpp);
+}
+
+__global__ void __launch_bounds__(512, 2)
+mufreq_lookup_smem_kernel(int64_t N, const double2* __restrict__ F2,
+                          const double2* __restrict__ R2, int nr, int nm, double wr, double wm,
+                          double cell, double ploidy, double adr,
+                          const __grid_constant__ CnModel m, const double* __restrict__ lpp8,
+                          const unsigned short* __restrict__ code16, double* __restrict__ out) {
+  extern __shared__ __align__(16) double sm[];
+  const int n = nr * nm, n8 = (n + 1) & ~1, n16 = (n + 7) & ~7;  // padded to 16 bytes
+  double* s_lpp = sm;
+  unsigned short* s_code = reinterpret_cast<unsigned short*>(sm + n8);
+  double* probr = reinterpret_cast<double*>(s_code + n16);
+  double* mm = probr + m.nc;
+  {
+    const int4* g = reinterpret_cast<const int4*>(lpp8);
+    int4* d = reinterpret_cast<int4*>(s_lpp);
+    for (int i = threadIdx.x; i < n8 / 2; i += blockDim.x) d[i] = g[i];
+    g = reinterpret_cast<const int4*>(code16);
+    d = reinterpret_cast<int4*>(s_code);
+    for (int i = threadIdx.x; i < n16 / 8; i += blockDim.x) d[i] = g[i];
+  }
+  build_muf_model(m, cell, ploidy, adr, probr, mm);  // for the rare direct path
+  __syncthreads();
+  constexpr int U = 2;  // pairs per thread and iteration: four positions in flight
+  const int64_t NP = N >> 1, stride = (int64_t)gridDim.x * blockDim.x;
+  const double cnn = (double)m.CNn;
+  double2* o0 = reinterpret_cast<double2*>(out);
+  double2* o1 = reinterpret_cast<double2*>(out + N);
+  double2* o2 = reinterpret_cast<double2*>(out + 2 * N);
+  double2* o3 = reinterpret_cast<double2*>(out + 3 * N);
+  for (int64_t p0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p0 < NP; p0 += U * stride) {
+    double2 r[U], f[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t p = p0 + u * stride;
+      r[u] = p < NP ? __ldcs(R2 + p) : make_double2(1.0, 1.0);
+      f[u] = p < NP ? __ldcs(F2 + p) : make_double2(0.0, 0.0);
+    }
+    double c1[2 * U], c2[2 * U], c3[2 * U], lp[2 * U];
+    unsigned rare = 0;
+#pragma unroll
+    for (int u = 0; u < 2 * U; ++u) {
+      const double rr = (u & 1) ? r[u >> 1].y : r[u >> 1].x;
+      const double ff = (u & 1) ? f[u >> 1].y : f[u >> 1].x;
+      const double kr = nearbyint(wr * (rr / (1 + rr)));  // R/bayes.R:26
+      const double km = nearbyint(ff * wm);               // R/bayes.R:4
+      const bool in = kr >= 0.0 && kr < (double)nr && km >= 0.0 && km < (double)nm;
+      const int idx = in ? (int)kr * nm + (int)km : 0;
+      const unsigned cd = s_code[idx];
+      const bool ok = cd != kMufNaCode;
+      c1[u] = ok ? cnn : na_real();
+      c2[u] = ok ? small_uint_to_double(cd >> 8) : na_real();
+      c3[u] = ok ? small_uint_to_double(cd & 255u) : na_real();
+      lp[u] = s_lpp[idx];
+      if (!in) rare |= 1u << u;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t p = p0 + u * stride;
+      if (p >= NP) continue;
+      __stcs(o0 + p, make_double2(c1[2 * u], c1[2 * u + 1]));
+      __stcs(o1 + p, make_double2(c2[2 * u], c2[2 * u + 1]));
+      __stcs(o2 + p, make_double2(c3[2 * u], c3[2 * u + 1]));
+      __stcs(o3 + p, make_double2(lp[2 * u], lp[2 * u + 1]));
+    }
+    // positions outside the table (NA, ratio < 0, F outside [0, 1]; rare): evaluated directly
+    // and written over the placeholder this thread has just stored
+    while (rare) {
+      const int u = __ffs((int)rare) - 1;
+      rare &= rare - 1;
+      const int64_t p = p0 + (u >> 1) * stride;
+      if (p >= NP) continue;
+      const int64_t sidx = 2 * p + (u & 1);
+      const double rr = reinterpret_cast<const double*>(R2)[sidx];
+      const double ff = reinterpret_cast<const double*>(F2)[sidx];
+      const double4 d = muf_direct(m, probr, mm, nearbyint(wr * (rr / (1 + rr))), wr,
+                                   nearbyint(ff * wm), wm);
+      out[sidx] = d.x;
+      out[N + sidx] = d.y;
+      out[2 * N + sidx] = d.z;
+      out[3 * N + sidx] = d.w;
+    }
+  }
+}
+
+static size_t muf_compact_bytes(int64_t n) {  // lpp8 + code16, each padded to 16 bytes
+  return (size_t)((n + 1) & ~(int64_t)1) * sizeof(double) +
+         (size_t)((n + 7) & ~(int64_t)7) * sizeof(unsigned short);
+}
+
 // number of table bytes sqz_mufreq_point_scalar_dev needs (0: weights not usable for the
 // table, the caller should use the vector-weight entry point)
 size_t mufreq_scalar_table_bytes(double wm, double wr) {
   if (!(wm >= 0) || !(wr >= 0) || wm != nearbyint(wm) || wr != nearbyint(wr)) return 0;
   if (wm > 4096 || wr > 4096 || (wm + 1) * (wr + 1) > 4.0e6) return 0;
   // answer table + the two score tables of stage 1, sized for any copy-number range
+  // + the compact copy of the answers for the shared-memory lookup
   return (size_t)((wm + 1) * (wr + 1)) * sizeof(double4) +
          (size_t)(wr + 1) * kMaxCN * sizeof(double) +
-         (size_t)(wm + 1) * kMaxTypes * sizeof(double);
+         (size_t)(wm + 1) * kMaxTypes * sizeof(double) +
+         muf_compact_bytes((int64_t)((wm + 1) * (wr + 1)));
 }
 
 int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t N, double wm,
@@ -495,17 +641,34 @@ int mufreq_point_scalar_launch(const double* d_F, const double* d_ratio, int64_t
   const size_t smb = (size_t)(m.nc + m.T) * sizeof(double);
   double* srp = (double*)((char*)table + (size_t)nr * nm * sizeof(double4));
   double* smv = srp + (size_t)nr * kMaxCN;
+  double* lpp8 = smv + (size_t)nm * kMaxTypes;
+  const int64_t npair = (int64_t)nr * nm;
+  unsigned short* code16 = reinterpret_cast<unsigned short*>(lpp8 + ((npair + 1) & ~(int64_t)1));
   int64_t sb = ((int64_t)nr * m.nc + (int64_t)nm * m.T + 127) / 128;
   if (sb > 148 * 16) sb = 148 * 16;
   mufreq_scores_kernel<<<(unsigned)sb, 128, smb, st>>>(nr, nm, wr, wm, cellularity, ploidy, adr,
                                                       m, srp, smv);
   SQZ_CUDA(cudaGetLastError());
-  int64_t tb = ((int64_t)nr * nm + 127) / 128;
+  int64_t tb = (npair * 32 + 255) / 256;  // one warp per pair of counts
   if (tb > 148 * 16) tb = 148 * 16;
-  mufreq_table_kernel<<<(unsigned)tb, 128, 0, st>>>(nr, nm, m, srp, smv, (double4*)table);
+  mufreq_table_kernel<<<(unsigned)tb, 256, 0, st>>>(nr, nm, m, srp, smv, (double4*)table, lpp8,
+                                                   code16);
   SQZ_CUDA(cudaGetLastError());
   const bool vec2 = (N % 2 == 0) &&
                     !(((uintptr_t)d_F | (uintptr_t)d_ratio | (uintptr_t)d_out) & 15);
+  // compact table in shared memory: two CTAs of 512 threads per SM when it fits half an SM
+  const size_t smem_tab = muf_compact_bytes(npair) + smb;
+  static const bool no_smem_tab = getenv("SQZ_MUFREQ_NO_SMEM") != nullptr;
+  if (vec2 && !no_smem_tab && N >= (1 << 16) && smem_tab <= 112 * 1024 &&
+      CNt_max <= 255) {
+    SQZ_CUDA(cudaFuncSetAttribute(mufreq_lookup_smem_kernel,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tab));
+    mufreq_lookup_smem_kernel<<<148 * 2, 512, smem_tab, st>>>(
+        N, (const double2*)d_F, (const double2*)d_ratio, nr, nm, wr, wm, cellularity, ploidy,
+        adr, m, lpp8, code16, d_out);
+    SQZ_CUDA(cudaGetLastError());
+    return SQZ_OK;
+  }
   int64_t blocks = ((vec2 ? N / 2 : N) + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
   if (vec2)

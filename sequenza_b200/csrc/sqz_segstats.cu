@@ -8,18 +8,20 @@
 // output of unique.breaks (R/segments.R:133-139), increasing inside a chromosome.  A segment
 // is then a contiguous run of rows, found by two binary searches.
 //
-//   segstat_reduce_kernel  one CTA per segment, ONE pass over its rows: counts, the weighted
-//                          sums, and sum / sum of squares in double-double (106 bits), from
-//                          which var = (S2 - S1^2 / n) / (n - 1) comes out to ~1e-30 (mean^2 /
-//                          var + 1) relative -- R's two-pass var() to far below the 1e-12 the
-//                          tests ask; identical values give exactly 0, as two passes do.  Also
-//                          what the density needs (n, sum of good.reads, sd / min / max of
-//                          c(Bf, Af)).  At most 49 bytes per row: HBM-bound.
+//   segstat_reduce_kernel  one CTA per segment, ONE pass over its rows: N.ratio, the weighted
+//                          sums of the depth ratio, and sum / sum of squares in double-double
+//                          (106 bits), from which var = (S2 - S1^2 / n) / (n - 1) comes out
+//                          to ~1e-30 (mean^2 / var + 1) relative -- R's two-pass var() to far
+//                          below the 1e-12 the tests ask; identical values give exactly 0, as
+//                          two passes do.  At most 49 bytes per row: HBM-bound.
 //                          The het rows' (Bf, Af, good.reads) are copied next to each other
-//                          into the workspace (any order: everything downstream is
-//                          order-independent), so the density kernel streams 24 bytes per het
-//                          row instead of re-reading 25 bytes of every row.
-//   segstat_kde_kernel     one CTA per segment with at least two het positions:
+//                          into the workspace (warp-aggregated slots, any order: everything
+//                          downstream is order-independent), so that what concerns the B
+//                          allele runs on full warps in the next kernel instead of on the 30 %
+//                          of the lanes that hold a het row.
+//   segstat_kde_kernel     one CTA per segment with at least two het positions: N.BAF's
+//                          companions (sd.BAF; n, sum of good.reads, sd / min / max of
+//                          c(Bf, Af)) from the compact rows, then
 //                          quantile(type 7) by radix selection on the ordered bit patterns
 //                          (the four order statistics of the two quartiles in the same eight
 //                          passes),
@@ -50,11 +52,9 @@ struct SegArgs {
 
 // per segment, handed from the reduction to the density kernel
 struct SegMid {
-  int64_t lo, hi;   // its rows
-  int64_t nb;       // het rows with enough reads
-  double gsum;      // sum(good.reads) over them
-  double sdx;       // sd(c(Bf, Af))
-  double xmin, xmax, x0;  // range of c(Bf, Af) and its first element (Bf of the first row)
+  int64_t lo, hi;  // its rows
+  int64_t nb;      // het rows with enough reads
+  double x0;       // Bf of the first of them: x[1] of c(Bf, Af), bw.nrd0's last resort
 };
 
 // ---- double-double helpers -------------------------------------------------------------
@@ -96,50 +96,15 @@ __device__ __forceinline__ D2 d2_div(D2 a, double n) {  // a / n
   return D2{h, q2 - (h - q)};
 }
 
-template <int N>
-__device__ __forceinline__ void block_sum_d2(D2 (&v)[N], D2* red /* [N][8] */) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int k = 0; k < N; ++k) {
-    for (int off = 16; off; off >>= 1) {
-      D2 o;
-      o.hi = __shfl_xor_sync(0xffffffffu, v[k].hi, off);
-      o.lo = __shfl_xor_sync(0xffffffffu, v[k].lo, off);
-      v[k] = d2_merge(v[k], o);  // both partners compute hi + lo of the same pair in the same
-    }                            // order up to commutativity of the first addition
-    if (lane == 0) red[k * 8 + warp] = v[k];
-  }
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < N; ++k) {
-    D2 t = red[k * 8];
-    for (int w = 1; w < kSegThreads / 32; ++w) t = d2_merge(t, red[k * 8 + w]);
-    v[k] = t;
-  }
-  __syncthreads();
-}
-
-__device__ __forceinline__ long long block_sum_ll(long long v, long long* red) {
-  for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  long long t = 0;
-  for (int w = 0; w < kSegThreads / 32; ++w) t += red[w];
-  __syncthreads();
-  return t;
-}
-
-__device__ __forceinline__ double block_minmax(double v, bool is_max, double* red) {
-  for (int off = 16; off; off >>= 1) {
-    const double o = __shfl_xor_sync(0xffffffffu, v, off);
-    v = is_max ? fmax(v, o) : fmin(v, o);
-  }
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
-  __syncthreads();
-  double t = red[0];
-  for (int w = 1; w < kSegThreads / 32; ++w) t = is_max ? fmax(t, red[w]) : fmin(t, red[w]);
-  __syncthreads();
-  return t;
+// stats::sd = sqrt(var) from the sums, n - 1 in the denominator, NA below two values
+__device__ __forceinline__ double d2_sd(const D2& s1, const D2& s2, long long n, double mn,
+                                        double mx) {
+  if (n < 2) return na_real();
+  if (mn == mx) return 0.0;  // identical values: exactly zero, as the two-pass var gives
+  const D2 q = d2_div(d2_sq(s1), (double)n);
+  const D2 r = d2_add(d2_add(s2, -q.hi), -q.lo);
+  const double var = (r.hi + r.lo) / (double)(n - 1);
+  return sqrt(var > 0 ? var : 0.0);
 }
 
 // first index in [a, b) whose position is > x (positions sorted; b if none), by the whole
@@ -166,15 +131,16 @@ __device__ __forceinline__ int64_t block_upper_bound(const double* p, int64_t a,
 }  // namespace
 
 // ---- reductions of one segment (R/segments.R:140-170) -----------------------------------
-__global__ void __launch_bounds__(kSegThreads, 2)
+__global__ void __launch_bounds__(kSegThreads, 3)
 segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ cx,
                       double* __restrict__ cg, double* __restrict__ out) {
   __shared__ unsigned s_slot;
-  __shared__ D2 red[9 * 8];
-  __shared__ long long redl[8];
-  __shared__ double redd[8];
+  __shared__ D2 red[4 * 8];
+  __shared__ long long redl[3 * 8];
+  __shared__ double redd[2 * 8];
   __shared__ int s_first;
   const int64_t s = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int64_t c = 0;
   while (c + 1 < a.n_chr && a.seg_off[c + 1] <= s) ++c;
   const int64_t r0 = a.row_off[c], r1 = a.row_off[c + 1];
@@ -185,15 +151,14 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
   __syncthreads();
   const bool W = a.weighted != 0;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const double NaN = __longlong_as_double(0x7FF8000000000000LL);
 
-  // one pass: counts, sums and sums of squares
-  D2 sum[9] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
-  // 0 rw, 1 w.r, 2 v, 3 v^2, 4 vb, 5 vb^2, 6 good, 7 x, 8 x^2
-  long long nv = 0, nb = 0, nvb = 0, first = 0x7fffffffffffffffLL;
-  double vmin = INF, vmax = -INF, bmin = INF, bmax = -INF, xmin = INF, xmax = -INF;
-  auto row = [&](int64_t i, double r, double dn, double g, unsigned char het, double bf,
-                 double af) {
-    const bool hb = het && g >= a.min_reads;  // R/segments.R:128-129
+  // one pass: counts, sums and sums of squares of the depth ratio; het rows set aside
+  D2 sum[4] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};  // 0 rw, 1 w.r, 2 v, 3 v^2
+  long long nv = 0, nb = 0, first = 0x7fffffffffffffffLL;
+  double vmin = INF, vmax = -INF;
+  double2* cx2 = reinterpret_cast<double2*>(cx);  // the segment owns cx2[lo, hi) and cg[lo, hi)
+  auto row = [&](int64_t i, double r, double dn, double g, bool het, double bf, double af) {
     double v;
     if (W) {
       const double wr = sqrt(dn), rw = r * wr;  // R/segments.R:116-117
@@ -210,109 +175,99 @@ segstat_reduce_kernel(SegArgs a, SegMid* __restrict__ mid, double* __restrict__ 
       vmin = fmin(vmin, v);
       vmax = fmax(vmax, v);
     }
-    if (hb) {
-      double vb = bf;
-      if (W) {
-        const double wb = sqrt(g);  // R/segments.R:118-119
-        vb = (bf * wb) / wb;
+    // R/segments.R:128-129: het rows with enough reads go to the compact copy, one slot
+    // range per warp and batch row (every lane of the warp is here: uniform trip counts)
+    const bool hb = het && g >= a.min_reads;
+    const unsigned hm = __ballot_sync(0xffffffffu, hb);
+    if (hm) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&s_slot, (unsigned)__popc(hm));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (hb) {
+        const int64_t slot = lo + base + __popc(hm & ((1u << lane) - 1u));
+        cx2[slot] = make_double2(bf, af);
+        cg[slot] = g;
+        ++nb;
+        if (i < first) first = i;
       }
-      ++nb;
-      if (i < first) first = i;
-      if (!isnan(vb)) {
-        d2_acc(sum[4], vb);
-        d2_acc_sq(sum[5], vb);
-        ++nvb;
-        bmin = fmin(bmin, vb);
-        bmax = fmax(bmax, vb);
-      }
-      d2_acc(sum[6], g);
-      d2_acc(sum[7], bf);
-      d2_acc(sum[7], af);
-      d2_acc_sq(sum[8], bf);
-      d2_acc_sq(sum[8], af);
-      xmin = fmin(xmin, fmin(bf, af));
-      xmax = fmax(xmax, fmax(bf, af));
-      // compact copy for the density kernel: the segment owns cx[2 lo, 2 hi) and cg[lo, hi)
-      const unsigned slot = atomicAdd(&s_slot, 1u);
-      cx[2 * (lo + slot)] = bf;
-      cx[2 * (lo + slot) + 1] = af;
-      cg[lo + slot] = g;
     }
   };
   // four rows per thread in flight: the loads of a batch are issued before any of it is
-  // consumed (the kernel is bound by memory latency, not by bandwidth or arithmetic)
+  // consumed.  Rows past the end are read as NA / not het and change nothing.
   constexpr int kBatch = 4;
-  int64_t i = lo + threadIdx.x;
-  for (; i + (kBatch - 1) * (int64_t)kSegThreads < hi; i += kBatch * (int64_t)kSegThreads) {
+  for (int64_t b0 = lo; b0 < hi; b0 += kBatch * (int64_t)kSegThreads) {  // block-uniform
     double r[kBatch], dn[kBatch], g[kBatch], bf[kBatch], af[kBatch];
-    unsigned char het[kBatch];
+    bool het[kBatch];
 #pragma unroll
     for (int k = 0; k < kBatch; ++k) {
-      const int64_t ii = i + k * (int64_t)kSegThreads;
-      r[k] = a.ratio[ii];
-      dn[k] = W ? a.dnorm[ii] : 0.;
-      g[k] = a.good[ii];
-      het[k] = a.het[ii];
-      bf[k] = a.Bf[ii];
-      af[k] = a.Af[ii];
+      const int64_t ii = b0 + k * (int64_t)kSegThreads + threadIdx.x;
+      const bool in = ii < hi;
+      r[k] = in ? a.ratio[ii] : NaN;
+      dn[k] = in && W ? a.dnorm[ii] : NaN;
+      g[k] = in ? a.good[ii] : 0.;
+      het[k] = in && a.het[ii] != 0;
+      bf[k] = in ? a.Bf[ii] : 0.;
+      af[k] = in ? a.Af[ii] : 0.;
     }
 #pragma unroll
     for (int k = 0; k < kBatch; ++k)
-      row(i + k * (int64_t)kSegThreads, r[k], dn[k], g[k], het[k], bf[k], af[k]);
+      row(b0 + k * (int64_t)kSegThreads + threadIdx.x, r[k], dn[k], g[k], het[k], bf[k], af[k]);
   }
-  for (; i < hi; i += kSegThreads)
-    row(i, a.ratio[i], W ? a.dnorm[i] : 0., a.good[i], a.het[i], a.Bf[i], a.Af[i]);
 #pragma unroll
-  for (int k = 0; k < 9; ++k) sum[k] = d2_add(D2{sum[k].hi, 0.}, sum[k].lo);  // normal form
-  block_sum_d2(sum, red);
-  nv = block_sum_ll(nv, redl);
-  nb = block_sum_ll(nb, redl);
-  nvb = block_sum_ll(nvb, redl);
-  vmin = block_minmax(vmin, false, redd);
-  vmax = block_minmax(vmax, true, redd);
-  bmin = block_minmax(bmin, false, redd);
-  bmax = block_minmax(bmax, true, redd);
-  xmin = block_minmax(xmin, false, redd);
-  xmax = block_minmax(xmax, true, redd);
-  {  // the first het row of the segment: x[1] of c(Bf, Af), bw.nrd0's last resort
-    long long f = first;
-    for (int off = 16; off; off >>= 1) f = min(f, __shfl_xor_sync(0xffffffffu, f, off));
-    if ((threadIdx.x & 31) == 0) redl[threadIdx.x >> 5] = f;
-    __syncthreads();
-    first = redl[0];
-    for (int w = 1; w < kSegThreads / 32; ++w) first = min(first, redl[w]);
-    __syncthreads();
+  for (int k = 0; k < 4; ++k) sum[k] = d2_add(D2{sum[k].hi, 0.}, sum[k].lo);  // normal form
+  // Block totals, for thread 0 alone (it writes the segment's row): the chains go through
+  // the shuffle levels side by side, one barrier, thread 0 folds the eight warps' partials.
+#pragma unroll
+  for (int off = 16; off; off >>= 1) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      D2 o;
+      o.hi = __shfl_xor_sync(0xffffffffu, sum[k].hi, off);
+      o.lo = __shfl_xor_sync(0xffffffffu, sum[k].lo, off);
+      sum[k] = d2_merge(sum[k], o);
+    }
+    nv += __shfl_xor_sync(0xffffffffu, nv, off);
+    nb += __shfl_xor_sync(0xffffffffu, nb, off);
+    first = min(first, __shfl_xor_sync(0xffffffffu, first, off));
+    vmin = fmin(vmin, __shfl_xor_sync(0xffffffffu, vmin, off));
+    vmax = fmax(vmax, __shfl_xor_sync(0xffffffffu, vmax, off));
   }
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) red[k * 8 + warp] = sum[k];
+    redl[0 * 8 + warp] = nv;
+    redl[1 * 8 + warp] = nb;
+    redl[2 * 8 + warp] = first;
+    redd[0 * 8 + warp] = vmin;
+    redd[1 * 8 + warp] = vmax;
+  }
+  __syncthreads();
   if (threadIdx.x != 0) return;
-  // stats::sd = sqrt(var), n - 1 in the denominator, NA below two values
-  auto sd = [](const D2& s1, const D2& s2, long long n, double mn, double mxv) {
-    if (n < 2) return na_real();
-    if (mn == mxv) return 0.0;  // identical values: exactly zero, as the two-pass var gives
-    const D2 q = d2_div(d2_sq(s1), (double)n);
-    const D2 r = d2_add(d2_add(s2, -q.hi), -q.lo);
-    const double var = (r.hi + r.lo) / (double)(n - 1);
-    return sqrt(var > 0 ? var : 0.0);
-  };
+#pragma unroll
+  for (int w = 1; w < kSegThreads / 32; ++w) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) sum[k] = d2_merge(sum[k], red[k * 8 + w]);
+    nv += redl[0 * 8 + w];
+    nb += redl[1 * 8 + w];
+    first = min(first, redl[2 * 8 + w]);
+    vmin = fmin(vmin, redd[0 * 8 + w]);
+    vmax = fmax(vmax, redd[1 * 8 + w]);
+  }
   const D2 mv = nv > 0 ? d2_div(sum[2], (double)nv) : D2{0, 0};
   const int64_t S = a.S;
-  double bfo = na_real();
-  if (nb == 1) bfo = a.Bf[first];  // length(Bf) == 1 (R/model.R:93-94)
-  out[0 * S + s] = bfo;            // nb >= 2: the density kernel fills it in
-  out[1 * S + s] = (double)nb;
-  out[2 * S + s] = sd(sum[4], sum[5], nvb, bmin, bmax);
+  const double x0 = nb >= 1 ? a.Bf[first] : 0.0;
+  out[0 * S + s] = nb == 1 ? x0 : na_real();  // length(Bf) == 1 (R/model.R:93-94); nb >= 2:
+  out[1 * S + s] = (double)nb;                // the density kernel fills Bf and sd.BAF in
+  out[2 * S + s] = na_real();
   out[3 * S + s] = W ? (sum[0].hi + sum[0].lo) / (sum[1].hi + sum[1].lo)
-                     : (nv > 0 ? mv.hi + mv.lo : __longlong_as_double(0x7FF8000000000000LL));
+                     : (nv > 0 ? mv.hi + mv.lo : NaN);
   out[4 * S + s] = (double)(hi - lo);
-  out[5 * S + s] = sd(sum[2], sum[3], nv, vmin, vmax);
+  out[5 * S + s] = d2_sd(sum[2], sum[3], nv, vmin, vmax);
   SegMid m;
   m.lo = lo;
   m.hi = hi;
   m.nb = nb;
-  m.gsum = sum[6].hi + sum[6].lo;
-  m.sdx = nb >= 1 ? sd(sum[7], sum[8], 2 * nb, xmin, xmax) : 0.0;
-  m.xmin = xmin;
-  m.xmax = xmax;
-  m.x0 = nb >= 1 ? a.Bf[first] : 0.0;
+  m.x0 = x0;
   mid[s] = m;
 }
 
@@ -340,15 +295,19 @@ __device__ __forceinline__ double r_dnorm(double x, double sigma) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kSegThreads)
+__global__ void __launch_bounds__(kSegThreads, 4)
 segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __restrict__ cx,
                    const double* __restrict__ cg, double* __restrict__ out) {
   __shared__ unsigned hist[4][256];
   __shared__ unsigned long long s_prefix[4];
   __shared__ long long s_rank[4];
   __shared__ unsigned long long ybin[kDensN + 1];  // 2^-62 fixed point
-  __shared__ double K[kDensN + 1], kords[kDensN], gy[kDensN];
+  __shared__ double K[kDensN + 1], kords[kDensN], gy[kDensN];  // gy doubles as the bins in fp64
   __shared__ double s_q[4];
+  __shared__ D2 red[5 * 8];
+  __shared__ long long redl[8];
+  __shared__ double redd[4 * 8];
+  __shared__ double s_stat[4];  // sum(good.reads), sd / min / max of c(Bf, Af)
   const int64_t s = blockIdx.x;
   const SegMid m = mid[s];
   if (m.nb < 2) return;  // 0: NA, 1: Bf itself -- written by the reduction kernel
@@ -357,6 +316,87 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
 
   const double* x = cx + 2 * m.lo;  // c(Bf, Af) of the het rows, interleaved: N values
   const double* gw = cg + m.lo;     // good.reads of the same rows
+
+  // sd.BAF (R/segments.R:152-154) and what the density needs, from the compact rows: every
+  // lane holds a het row here.  Sums in double-double as in the reduction kernel.
+  {
+    const double INF = __longlong_as_double(0x7FF0000000000000LL);
+    const bool W = a.weighted != 0;
+    const double2* x2 = reinterpret_cast<const double2*>(x);
+    D2 sum[5] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};  // vb, vb^2, good, x, x^2
+    long long nvb = 0;
+    double bmin = INF, bmax = -INF, xmin = INF, xmax = -INF;
+    for (int64_t i = tid; i < m.nb; i += kSegThreads) {
+      const double2 v = x2[i];
+      const double g = gw[i];
+      double vb = v.x;
+      if (W) {
+        const double wb = sqrt(g);  // R/segments.R:118-119
+        vb = (v.x * wb) / wb;
+      }
+      if (!isnan(vb)) {
+        d2_acc(sum[0], vb);
+        d2_acc_sq(sum[1], vb);
+        ++nvb;
+        bmin = fmin(bmin, vb);
+        bmax = fmax(bmax, vb);
+      }
+      d2_acc(sum[2], g);
+      d2_acc(sum[3], v.x);
+      d2_acc(sum[3], v.y);
+      d2_acc_sq(sum[4], v.x);
+      d2_acc_sq(sum[4], v.y);
+      xmin = fmin(xmin, fmin(v.x, v.y));
+      xmax = fmax(xmax, fmax(v.x, v.y));
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) sum[k] = d2_add(D2{sum[k].hi, 0.}, sum[k].lo);  // normal form
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        D2 o;
+        o.hi = __shfl_xor_sync(0xffffffffu, sum[k].hi, off);
+        o.lo = __shfl_xor_sync(0xffffffffu, sum[k].lo, off);
+        sum[k] = d2_merge(sum[k], o);
+      }
+      nvb += __shfl_xor_sync(0xffffffffu, nvb, off);
+      bmin = fmin(bmin, __shfl_xor_sync(0xffffffffu, bmin, off));
+      bmax = fmax(bmax, __shfl_xor_sync(0xffffffffu, bmax, off));
+      xmin = fmin(xmin, __shfl_xor_sync(0xffffffffu, xmin, off));
+      xmax = fmax(xmax, __shfl_xor_sync(0xffffffffu, xmax, off));
+    }
+    const int lane = tid & 31, warp = tid >> 5;
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) red[k * 8 + warp] = sum[k];
+      redl[warp] = nvb;
+      redd[0 * 8 + warp] = bmin;
+      redd[1 * 8 + warp] = bmax;
+      redd[2 * 8 + warp] = xmin;
+      redd[3 * 8 + warp] = xmax;
+    }
+    __syncthreads();
+    if (tid == 0) {
+#pragma unroll
+      for (int w = 1; w < kSegThreads / 32; ++w) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) sum[k] = d2_merge(sum[k], red[k * 8 + w]);
+        nvb += redl[w];
+        bmin = fmin(bmin, redd[0 * 8 + w]);
+        bmax = fmax(bmax, redd[1 * 8 + w]);
+        xmin = fmin(xmin, redd[2 * 8 + w]);
+        xmax = fmax(xmax, redd[3 * 8 + w]);
+      }
+      out[2 * a.S + s] = d2_sd(sum[0], sum[1], nvb, bmin, bmax);  // column 2: sd.BAF
+      s_stat[0] = sum[2].hi + sum[2].lo;
+      s_stat[1] = d2_sd(sum[3], sum[4], N, xmin, xmax);
+      s_stat[2] = xmin;
+      s_stat[3] = xmax;
+    }
+    __syncthreads();
+  }
+  const double m_gsum = s_stat[0], m_sdx = s_stat[1], m_xmin = s_stat[2], m_xmax = s_stat[3];
 
   // quantile(x, c(.25, .75), type = 7): index = 1 + (n - 1) p; (1 - h) x[lo] + h x[hi].
   // The four order statistics by radix selection on the ordered bit patterns, 8 bits a
@@ -389,15 +429,41 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
       if (hi_bits == p3) atomicAdd(&hist[3][d], 1u);
     }
     __syncthreads();
-    if (tid < 4) {
-      long long r = s_rank[tid];
-      int b = 0;
-      while (b < 255 && r >= (long long)hist[tid][b]) {
-        r -= hist[tid][b];
-        ++b;
+    if (tid < 4 * 32) {
+      // warp w finds the digit of order statistic w: the bin where the running count passes
+      // the rank.  A lane sums its eight bins, a shuffle scan gives the count below the
+      // lane's bins, and the one lane whose bins hold the rank walks them.
+      const int w = tid >> 5, lane = tid & 31;
+      const long long r = s_rank[w];
+      unsigned c8[8], tot = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        c8[k] = hist[w][lane * 8 + k];
+        tot += c8[k];
       }
-      s_rank[tid] = r;
-      s_prefix[tid] |= (unsigned long long)b << shift;
+      unsigned incl = tot;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const unsigned o = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += o;
+      }
+      const long long below = (long long)(incl - tot);
+      // the rank is below the total of the candidates, so exactly one lane qualifies; a
+      // rank past the end (cannot happen) would leave the last bin, as the serial walk did
+      const bool mine = (r >= below && r < below + (long long)tot) ||
+                        (lane == 31 && r >= (long long)incl);
+      if (mine) {
+        long long rr = r - below;
+        int b = 0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k)
+          if (b == k && rr >= (long long)c8[k]) {
+            rr -= c8[k];
+            ++b;
+          }
+        s_rank[w] = rr;
+        s_prefix[w] |= (unsigned long long)(lane * 8 + b) << shift;
+      }
     }
     __syncthreads();
   }
@@ -412,16 +478,16 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
   }
   __syncthreads();
   // bw.nrd0: 0.9 min(sd, IQR / 1.34) n^-0.2, with its fall-backs for a zero spread
-  double lo_ = fmin(m.sdx, (s_q[1] - s_q[0]) / 1.34);
+  double lo_ = fmin(m_sdx, (s_q[1] - s_q[0]) / 1.34);
   if (!(lo_ != 0)) {
-    lo_ = m.sdx;
+    lo_ = m_sdx;
     if (!(lo_ != 0)) {
       lo_ = fabs(m.x0);
       if (!(lo_ != 0)) lo_ = 1.;
     }
   }
   const double bw = 0.9 * lo_ * pow((double)N, -0.2);
-  const double from = m.xmin - 3 * bw, to = m.xmax + 3 * bw;  // cut = 3
+  const double from = m_xmin - 3 * bw, to = m_xmax + 3 * bw;  // cut = 3
   const double lo = from - 4 * bw, up = to + 4 * bw;
   const int n = kDensN;
 
@@ -430,34 +496,58 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
   for (int d = tid; d <= n; d += kSegThreads) K[d] = r_dnorm(d * (2 * (up - lo) / (2 * n - 1)), bw);
   __syncthreads();
   {
-    const double xdelta = (up - lo) / (n - 1), two_sum = 2 * m.gsum;
+    const double xdelta = (up - lo) / (n - 1), two_sum = 2 * m_gsum;
     const double SC = 4611686018427387904.0;  // 2^62
-    for (int64_t i = tid; i < N; i += kSegThreads) {
-      const double w = gw[i >> 1] / two_sum, xv = x[i];
-      if (!isfinite(xv)) continue;
-      const double xpos = (xv - lo) / xdelta;
-      const int ix = (int)floor(xpos);
-      const double fx = xpos - ix;
-      if (0 <= ix && ix <= n - 2) {
-        atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
-        atomicAdd(&ybin[ix + 1], (unsigned long long)(w * fx * SC + 0.5));
-      } else if (ix == -1) {
-        atomicAdd(&ybin[0], (unsigned long long)(w * fx * SC + 0.5));
-      } else if (ix == n - 1) {
-        atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+    const double2* x2 = reinterpret_cast<const double2*>(x);  // (Bf, Af) of a het row
+    for (int64_t i = tid; i < m.nb; i += kSegThreads) {
+      const double w = gw[i] / two_sum;  // the same weight for both values of the row
+      const double2 xv2 = x2[i];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const double xv = h ? xv2.y : xv2.x;
+        if (!isfinite(xv)) continue;
+        const double xpos = (xv - lo) / xdelta;
+        const int ix = (int)floor(xpos);
+        const double fx = xpos - ix;
+        if (0 <= ix && ix <= n - 2) {
+          atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+          atomicAdd(&ybin[ix + 1], (unsigned long long)(w * fx * SC + 0.5));
+        } else if (ix == -1) {
+          atomicAdd(&ybin[0], (unsigned long long)(w * fx * SC + 0.5));
+        } else if (ix == n - 1) {
+          atomicAdd(&ybin[ix], (unsigned long long)(w * (1 - fx) * SC + 0.5));
+        }
       }
     }
   }
   __syncthreads();
+  // the bins as doubles, once (the same value the conversion inside the sum gave: the
+  // 64-bit integer rounded to 53 bits, times 2^-62 exactly); gy is free until approx() below
+  for (int j = tid; j < n; j += kSegThreads)
+    gy[j] = (double)ybin[j] * (1.0 / 4611686018427387904.0);
+  __syncthreads();
   // the correlation of the bins with dnorm(kords) (R: fft(fft(y) * Conj(fft(kords)))): the
   // kernel is symmetric and only the first n bins are occupied, so K[|m - j|] is all of it
-  for (int j = tid; j < n; j += kSegThreads) {
-    double acc = 0.;
+  // A thread takes two neighbouring outputs: their kernel values are one apart, so a step of
+  // the sum loads one bin and one kernel value for two products.  Every output still adds
+  // its terms in increasing bin order, empty bins skipped, as before.
+  static_assert(kDensN == 2 * kSegThreads, "two outputs per thread");
+  {
+    const int j0 = 2 * tid;  // outputs j0 and j0 + 1
+    double acc0 = 0., acc1 = 0.;
+    double kprev = K[j0 + 1];  // K[|mm - (j0 + 1)|] at mm = 0
     for (int mm = 0; mm < n; ++mm) {
-      const unsigned long long yb = ybin[mm];
-      if (yb) acc += ((double)yb * (1.0 / 4611686018427387904.0)) * K[mm > j ? mm - j : j - mm];
+      const int d0 = mm > j0 ? mm - j0 : j0 - mm;
+      const double k0 = K[d0];  // = K[|mm - j0|]; the next step's K[|mm + 1 - (j0 + 1)|]
+      const double y = gy[mm];
+      if (y != 0.) {
+        acc0 += y * k0;
+        acc1 += y * kprev;
+      }
+      kprev = k0;
     }
-    kords[j] = acc > 0 ? acc : 0;
+    kords[j0] = acc0 > 0 ? acc0 : 0;
+    kords[j0 + 1] = acc1 > 0 ? acc1 : 0;
   }
   __syncthreads();
   // approx(xords, kords, seq(from, to, length.out = n))
