@@ -301,6 +301,7 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
   __shared__ unsigned hist[4][256];
   __shared__ unsigned long long s_prefix[4];
   __shared__ long long s_rank[4];
+  __shared__ unsigned s_cnt[4], s_ncand[4];
   __shared__ unsigned long long ybin[kDensN + 1];  // 2^-62 fixed point
   __shared__ double K[kDensN + 1], kords[kDensN], gy[kDensN];  // gy doubles as the bins in fp64
   __shared__ double s_q[4];
@@ -455,17 +456,59 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
       if (mine) {
         long long rr = r - below;
         int b = 0;
+        unsigned cb = c8[0];
 #pragma unroll
         for (int k = 0; k < 7; ++k)
           if (b == k && rr >= (long long)c8[k]) {
             rr -= c8[k];
             ++b;
+            cb = c8[k + 1];
           }
         s_rank[w] = rr;
         s_prefix[w] |= (unsigned long long)(lane * 8 + b) << shift;
+        s_cnt[w] = cb;  // values that share the digits found so far
       }
     }
     __syncthreads();
+    // Once few values are left around each of the four order statistics (three passes
+    // usually: 24 leading bits), they are gathered and ranked directly instead of walking
+    // all values five more times.  Many equal values keep a bin full: the passes go on.
+    constexpr unsigned kCand = 128;  // per order statistic, in the histogram's memory
+    if (shift <= 40 && shift > 0 &&
+        max(max(s_cnt[0], s_cnt[1]), max(s_cnt[2], s_cnt[3])) <= kCand) {
+      unsigned long long* cand = reinterpret_cast<unsigned long long*>(&hist[0][0]);
+      static_assert(sizeof(hist) >= 4 * kCand * sizeof(unsigned long long), "candidate lists");
+      if (tid < 4) s_ncand[tid] = 0;
+      __syncthreads();
+      const unsigned long long fixed = ~0ULL << shift;
+      const unsigned long long q0 = s_prefix[0], q1 = s_prefix[1], q2 = s_prefix[2],
+                               q3 = s_prefix[3];
+      for (int64_t i = tid; i < N; i += kSegThreads) {
+        const unsigned long long k = dkey(x[i]), hb = k & fixed;
+        if (hb == q0) cand[0 * kCand + atomicAdd(&s_ncand[0], 1u)] = k;
+        if (hb == q1) cand[1 * kCand + atomicAdd(&s_ncand[1], 1u)] = k;
+        if (hb == q2) cand[2 * kCand + atomicAdd(&s_ncand[2], 1u)] = k;
+        if (hb == q3) cand[3 * kCand + atomicAdd(&s_ncand[3], 1u)] = k;
+      }
+      __syncthreads();
+      if (tid < 4 * 32) {
+        const int w = tid >> 5, lane = tid & 31;
+        const int nc = (int)s_ncand[w];
+        const long long r = s_rank[w];
+        const unsigned long long* cw = cand + w * kCand;
+        for (int c = lane; c < nc; c += 32) {
+          const unsigned long long kc = cw[c];
+          long long rank = 0;
+          for (int j = 0; j < nc; ++j) {
+            const unsigned long long kj = cw[j];
+            rank += (kj < kc || (kj == kc && j < c)) ? 1 : 0;
+          }
+          if (rank == r) s_prefix[w] = kc;
+        }
+      }
+      __syncthreads();
+      break;
+    }
   }
   if (tid < 2) {
     const double xl = dunkey(s_prefix[2 * tid]), xh = dunkey(s_prefix[2 * tid + 1]);
@@ -536,6 +579,7 @@ segstat_kde_kernel(SegArgs a, const SegMid* __restrict__ mid, const double* __re
     const int j0 = 2 * tid;  // outputs j0 and j0 + 1
     double acc0 = 0., acc1 = 0.;
     double kprev = K[j0 + 1];  // K[|mm - (j0 + 1)|] at mm = 0
+#pragma unroll 4
     for (int mm = 0; mm < n; ++mm) {
       const int d0 = mm > j0 ? mm - j0 : j0 - mm;
       const double k0 = K[d0];  // = K[|mm - j0|]; the next step's K[|mm + 1 - (j0 + 1)|]
