@@ -698,8 +698,9 @@ def run_other(args, env, local_rank):
                              "api": "sequenza_b200.mufreq_bayes -> sqz_mufreq_point_scalar "
                                     "(pageable numpy arrays in and out)"},
                         gpu_launches=3 * steps,
-                        roofline={"bound": "hbm", "kernel": "mufreq_lookup_kernel (+ scores and "
-                                  "table kernels: two small launches)",
+                        roofline={"bound": "hbm",
+                                  "kernel": "mufreq_lookup_smem_kernel (+ scores and table "
+                                            "kernels: two small launches)",
                                   "achieved": 48.0 * n / (ms * 1e-3) / 1e9, "peak": peak,
                                   "unit": "GB/s", "frac": 48.0 * n / (ms * 1e-3) / 1e9 / peak,
                                   "peak_source": peak_src, "traffic": None,

@@ -4,10 +4,13 @@
 Bars (BASELINE.json): CNt / A / B and the selected (cellularity, ploidy) bit-exact; LPP
 within 1e-9 relative in fp64 (per-segment LPP, per-grid-point sums, and the normalised
 lpp matrix wherever it is above 1e-290)."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
 import sequenza_b200 as S
+from sequenza_b200 import _lib
 from sequenza_b200.synth import baf_args, synth_segments
 
 pytestmark = pytest.mark.gpu
@@ -366,6 +369,40 @@ def test_grid_column_lane_kernel(oracle, monkeypatch, n_seg, grid, cn_max):
                               CNt_max=cn_max, **baf_args(other))
         np.testing.assert_allclose(fits[1]["lpp"], one["lpp"], rtol=1e-9, atol=1e-300)
         np.testing.assert_array_equal(fits[0]["lpp"], fits[2]["lpp"])
+
+
+@pytest.mark.parametrize("scale", [1e-2, 1e-5, 1e-9, 1e-21, 1e3])
+def test_column_lane_kernel_fp32_bounds_at_extreme_scales(oracle, monkeypatch, scale):
+    """The column-per-lane kernel for CNt 0..7 takes its candidate bounds in fp32, rounded
+    downwards (sqz_baf_colwarp.cu).  Standard deviations scaled far down make the
+    standardised residuals, the BAF factors and the first candidate's maximum leave the
+    range (and the precision) of a float; scaled up, every copy number is a candidate.  A
+    bound that is too high would drop the true minimum: the sums must still equal the
+    oracle's, or the grid point must have been handed to the faithful kernel."""
+    monkeypatch.setenv("SQZ_COLWARP", "1")
+    ce, pl = np.linspace(0.1, 1.0, 64), S.r_seq(1, 7, 0.05)
+    seg = synth_segments(600, seed=77)
+    seg["sd_ratio"] = seg["sd_ratio"] * scale
+    seg["sd_Bf"] = seg["sd_Bf"] * (scale if scale > 1e-12 else scale * 1e-20)
+    # a few segments that sit exactly on a model value, and some far away from all of them
+    seg["depth_ratio"][:5] = [0.5, 1.0, 1.5, 2.0, 1e-3]
+    seg["depth_ratio"][5:8] = [37.0, 1e4, 4e-8]
+    kw = dict(cellularity=ce, ploidy=pl, priors_table=PRI)
+    L = _lib.lib()
+    L.sqz_profile_enable(1)
+    try:
+        got = S.baf_grid_sums(**baf_args(seg), **kw)
+        path, n_eval, launches = C.c_int(-1), C.c_ulonglong(0), C.c_longlong(0)
+        L.sqz_profile_counters(C.byref(path), C.byref(n_eval), C.byref(launches))
+    finally:
+        L.sqz_profile_enable(0)
+    assert path.value == 3
+    ref = oracle.baf_grid_sums(**baf_args(seg), **kw)
+    fin = np.isfinite(ref)
+    assert np.array_equal(np.isfinite(got), fin)
+    assert fin.any()
+    assert np.max(np.abs(got[fin] - ref[fin]) / np.abs(ref[fin])) <= 1e-9
+    assert int(np.nanargmax(got)) == int(np.nanargmax(ref))
 
 
 def test_full_size_properties_config3():
