@@ -144,7 +144,38 @@ def flops(tag):
     out.append("\nPer evaluation (%.4g evaluations per fit): **%.2f flops, %.2f fp64-pipe thread "
                "instructions** from the counters.  bench.py's analytic model "
                "(`roofline.flops_per_eval_executed`, `fp64_issue_slots_per_eval`) is checked "
-               "against these in `profiles/r02_summary.md`.\n" % (ev, tot_f / ev, 32 * tot_i / ev))
+               "against these in DESIGN.md 4.1.\n" % (ev, tot_f / ev, 32 * tot_i / ev))
+
+
+def other(path, title, cmd, bytes_note):
+    """launch list with DRAM bytes of a secondary workload (committed CSV under profiles/)"""
+    if not os.path.exists(path):
+        return
+    rows = [r for r in csv.reader(open(path)) if len(r) > 5]
+    hdr = [r for r in rows if "Metric Name" in r][0]
+    ik, im, iv, iid = (hdr.index(c) for c in ("Kernel Name", "Metric Name", "Metric Value", "ID"))
+    per = collections.OrderedDict()
+    for r in rows:
+        if r is hdr:
+            continue
+        per.setdefault((r[iid], r[ik].split("(")[0]), {})[r[im]] = float(r[iv].replace(",", ""))
+    agg = collections.OrderedDict()
+    for (_, k), d in per.items():
+        a = agg.setdefault(k, {"n": 0, "ns": 0.0, "rd": 0.0, "wr": 0.0})
+        a["n"] += 1
+        a["ns"] += d.get("gpu__time_duration.sum", 0.0)
+        a["rd"] += d.get("dram__bytes_read.sum", 0.0)
+        a["wr"] += d.get("dram__bytes_write.sum", 0.0)
+    out.append("## Launch list, %s\n" % title)
+    out.append("`%s` (`%s`). %s\n" % (cmd, path, bytes_note))
+    out.append("| kernel | launches | avg us | DRAM read MB | DRAM write MB | DRAM GB/s |")
+    out.append("|---|---|---|---|---|---|")
+    for k, a in agg.items():
+        n = a["n"]
+        out.append("| `%s` | %d | %.1f | %.1f | %.1f | %.0f |" % (
+            k.replace("void ", "").replace("sqz::", ""), n, a["ns"] / n / 1e3, a["rd"] / n / 1e6,
+            a["wr"] / n / 1e6, (a["rd"] + a["wr"]) / a["ns"] if a["ns"] else 0.0))
+    out.append("")
 
 
 traffic = {}
@@ -154,6 +185,18 @@ for tag in ("c3", "c2"):
     if t:
         traffic["config%s" % tag[1]] = t
     flops(tag)
+M3 = "ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum " \
+     "--clock-control none"
+other("profiles/r02_launches_config4.csv",
+      "config 4 (mufreq.bayes, 1e7 positions, scalar weights 100 / 100, T = 230)",
+      M3 + " -k regex:mufreq -c 12 python bench.py --workload config4",
+      "Algorithmic bytes of the lookup: 16 B in + 32 B out per position = 480 MB (part of the "
+      "output is still in L2 when the kernel ends).")
+other("profiles/r02_launches_segstats.csv",
+      "segment statistics (2.4e7 seqz rows, 2,400 segments, 30 % het)",
+      M3 + " -k regex:segstat -c 8 python bench.py --workload segstats",
+      "Algorithmic bytes of the reduction: 49 B per row = 1.18 GB; it also writes the compact "
+      "copy of the het rows (24 B each) that the density kernel reads back.")
 if traffic:
     json.dump(traffic, open("profiles/r02_traffic.json", "w"), indent=1)
 open("profiles/r02_ncu_summary.md", "w").write("\n".join(out) + "\n")
