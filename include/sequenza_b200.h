@@ -54,7 +54,10 @@ int sqz_release(void);
  * lpp_sum_out[ic * nP + ip] = sum(baf.bayes(cellularity[ic], ploidy[ip], ...)[, 4]),
  * i.e. result$LPP in expand.grid(ploidy, cellularity) order (R/bayes.R:106-107, :116).
  * The tapply / LogSumLik / exp steps (R/bayes.R:117-123) stay in R.
- * n_gpus >= 1: cellularity columns are split over that many devices of this process.
+ * n_gpus >= 1: the grid is dealt to that many devices of this process in whole units
+ * (tiles of columns x ploidies planned from the whole grid, so the result has the same
+ * bits for any n_gpus); the segment table reaches device 0 once and the others over NVLink,
+ * and every device stores its results into device 0's buffer.
  * --------------------------------------------------------------------------------- */
 int sqz_baf_grid(const double* Bf, const double* depth_ratio, const double* sd_Bf,
                  const double* sd_ratio, const double* weight_Bf,
@@ -67,7 +70,7 @@ int sqz_baf_grid(const double* Bf, const double* depth_ratio, const double* sd_B
 /* Cohort form of B1 (BASELINE config 5): S samples share one grid.  Sample k owns
  * segments seg_offsets[k] .. seg_offsets[k+1]-1 of the concatenated vectors and
  * avg_depth_ratio[k]; lpp_sum_out is S x (nC*nP), sample-major.  One launch per device;
- * with n_gpus > 1 and S >= n_gpus the cohort is split by sample, not by column. */
+ * with n_gpus > 1 and S >= n_gpus the cohort is split by sample, not by unit. */
 int sqz_baf_grid_batch(int64_t S, const int64_t* seg_offsets, const double* Bf,
                        const double* depth_ratio, const double* sd_Bf,
                        const double* sd_ratio, const double* weight_Bf,

@@ -95,3 +95,34 @@ def test_mufreq_scalar_table_path_equals_vector_path(oracle):
     a = S.mufreq_bayes(f[6:50], r[6:50], 0.7, 2.4, 1.0, 10.5, 100)
     c = oracle.mufreq_bayes(f[6:50], r[6:50], 0.7, 2.4, 1.0, 10.5, 100)
     assert same(a[:, 1], c[:, 1]) and same(a[:, 3], c[:, 3])
+
+
+@pytest.mark.parametrize("n", [70000, 70001])
+def test_mufreq_scalar_table_in_shared_memory(oracle, n):
+    """From 65,536 positions on (even count, aligned vectors) the lookup keeps the compact
+    answer table in shared memory (mufreq_lookup_smem_kernel); an odd count takes the
+    global-memory lookup.  Both against the direct kernel on every row -- positions outside
+    the table spread over the vector so that every thread role meets some -- and against the
+    oracle on a sample."""
+    mut = synth_mutations(n, seed=23)
+    f, r = mut["mufreq"].copy(), mut["depth_ratio"].copy()
+    rng = np.random.default_rng(5)
+    idx = rng.choice(n, 400, replace=False)
+    f[idx[:100]] = np.nan
+    r[idx[100:200]] = np.nan
+    f[idx[200:300]] = rng.choice([1.2, -0.1, 7.0], 100)
+    r[idx[300:400]] = rng.choice([-0.5, -2.0, 1e300], 100)
+    for wm, wr, cn_max in ((100, 100, 20), (100, 100, 7), (37, 250, 7)):
+        a = S.mufreq_bayes(f, r, 0.7, 2.4, 1.0, wm, wr, CNt_max=cn_max, priors_table=PRI)
+        b = S.mufreq_bayes(f, r, 0.7, 2.4, 1.0, np.full(n, float(wm)), np.full(n, float(wr)),
+                           CNt_max=cn_max, priors_table=PRI)
+        for col in range(4):
+            assert same(a[:, col], b[:, col]), (wm, wr, col)
+        sub = np.concatenate([idx, np.arange(0, n, 97)])
+        c = oracle.mufreq_bayes(f[sub], r[sub], 0.7, 2.4, 1.0, wm, wr, CNt_max=cn_max,
+                                priors_table=PRI)
+        for col in range(3):
+            assert same(a[sub, col], c[:, col]), (wm, wr, col)
+        ok = (a[sub, 3] == c[:, 3]) | (np.isnan(a[sub, 3]) & np.isnan(c[:, 3])) | \
+             (np.abs(a[sub, 3] - c[:, 3]) <= RTOL * np.abs(c[:, 3]))
+        assert ok.all()
