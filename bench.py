@@ -177,6 +177,19 @@ def ncu_traffic(workload, kernel_path):
         return None, "no capture committed for this workload"
 
 
+def ncu_instructions(workload, kernel_path):
+    """Warp instructions one launch of the dominant kernel executes (same capture as
+    ncu_traffic), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            e = json.load(f)[workload]
+        if int(e["kernel_path"]) != int(kernel_path):
+            return None
+        return float(e["warp_instructions_per_launch"])
+    except Exception:
+        return None
+
+
 def cpu_baseline(w, steps=1, warmup=0):
     """The oracle (CPU restatement, all host threads) on a bounded contiguous block of
     this workload's grid points.  Returns (evals/s, description dict, seconds per step)."""
@@ -493,6 +506,15 @@ def roofline_block(w, m, peak, world, local_rank):
     ref_flops = 11.0 * n_c + 13.0 * T  # reference formulation
     ref_logs = n_c + T
     traffic, traffic_src = ncu_traffic(w["name"], kpath) if world == 1 else (None, "N > 1")
+    winst = ncu_instructions(w["name"], kpath) if world == 1 else None
+    # what bounds the column-per-lane kernel since its bounds moved to fp32: instruction issue
+    # (one warp instruction per scheduler and cycle; the pre-pass is included in kernel_ms)
+    sm_hz = 1e6 * float(m.get("sm_mhz") or 1965.0)
+    issue = {"warp_instructions_per_launch": winst,
+             "achieved_per_scheduler_cycle": winst / (fast_ms * 1e-3 * 148 * 4 * sm_hz),
+             "peak": 1.0, "source": traffic_src,
+             "note": "grid kernel alone, ncu at the capture: smsp__issue_active in "
+                     "profiles/r02_ncu_summary.md"} if winst and fast_ms > 0 else None
     return {
         "bound": "fp64",
         "kernel": "%s<%d> (+ baf_colterm%s pre-pass)" % (
@@ -506,6 +528,10 @@ def roofline_block(w, m, peak, world, local_rank):
         "kernel_share_of_step": fast_ms / m["ms_per_step"] if m["ms_per_step"] else None,
         "fp64_issue_slots_per_eval": inst, "flops_per_eval_executed": flop,
         "fp32_flops_per_eval_executed": f32,
+        "frac_note": "fp64 flops only: the candidate bounds of the CNt 0..7 kernel run in fp32 "
+                     "since round 2 (fp64 flops per evaluation 9.88 -> 7.63), so the fraction "
+                     "fell while the fit got faster; `issue` is the resource that binds",
+        "issue": issue,
         "pipe_util": (local_evals * inst / (fast_ms * 1e-3)) / (peak * 1e12 / 2)
         if fast_ms > 0 and peak else None,
         "math_issue_slots_per_eval": math,

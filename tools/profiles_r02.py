@@ -106,6 +106,9 @@ def full(tag):
             "dram_bytes_per_launch": gb("dram__bytes_read.sum") + gb("dram__bytes_write.sum"),
             "dram_bytes_read": gb("dram__bytes_read.sum"),
             "dram_bytes_write": gb("dram__bytes_write.sum"),
+            "warp_instructions_per_launch": float(m["smsp__inst_executed.sum"][1].replace(",", "")),
+            "issue_active_pct": float(
+                m["smsp__issue_active.avg.pct_of_peak_sustained_active"][1].replace(",", "")),
             "source": "ncu --set full --clock-control none, one launch"}
 
 
