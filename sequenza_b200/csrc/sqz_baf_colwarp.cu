@@ -170,7 +170,13 @@ baf_colterm_cg8_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tot
 // (Measured and dropped: two warps sharing a CTA's tile, 16 ploidies and half of a stage's
 // analyses each, handed over in shared memory -- 128 registers, four warps per scheduler:
 // 31.4 ms on config 3 against 31.3 for one warp; with three per scheduler at 168 registers
-// the same.  More warps do not help: the kernel is bound by issue, not by latency.)
+// the same.  More warps do not help: the kernel is bound by issue, not by latency.
+// Also measured and dropped: the two phases on two warps of a CTA -- an analyst that requests
+// and analyses the stages one ahead and an evaluator that only streams the fp64 work, meeting
+// on mbarriers over a ring of three stages, four such CTAs per SM with the evaluators spread
+// over the schedulers by %warpid: 37.2 ms.  A lone evaluator warp per scheduler reaches 2.7
+// cycles per DFMA in the one-candidate loop but loses the time between segments and in the
+// two-candidate loop that a second warp of the same kind fills here.)
 template <int PT, int NC, int SB, int OCC, bool F32>
 __global__ void __launch_bounds__(32, OCC)
 baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg, int ic0,
