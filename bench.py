@@ -704,6 +704,18 @@ def run_other(args, env, local_rank):
             te = time.perf_counter()
             host = S.mufreq_bayes(mut["mufreq"], mut["depth_ratio"], 0.7, 2.4, 1.0, CNt_max=20)
             te = time.perf_counter() - te
+            # the same call on PINNED host vectors handed to the _dev entry point as they are
+            # (unified addressing: the kernel reads the inputs and writes the N x 4 result
+            # over PCIe, no staging copy) -- what SURVEY 8(e) suggests for the 320 MB result
+            fp = torch.from_numpy(mut["mufreq"]).pin_memory()
+            rp = torch.from_numpy(mut["depth_ratio"]).pin_memory()
+            op = torch.empty(4 * n, dtype=torch.float64).pin_memory()
+            ms_pin = timed_ms(torch, lambda: _lib.check(L.sqz_mufreq_point_scalar_dev(
+                fp.data_ptr(), rp.data_ptr(), n, 100.0, 100.0, 0.7, 2.4, 1.0, 1, 20, 2,
+                None, None, 0, tptr, tb, stream, op.data_ptr())), 5, 2)
+            torch.cuda.synchronize()
+            pin_ok = bool(np.array_equal(op.numpy().reshape(4, n).T[:, :3], host[:, :3],
+                                         equal_nan=True))
             ns = 200_000  # CPU sample: ~10-20 s single thread at T = 230
             tc = time.perf_counter()
             ref = O.mufreq_bayes(mut["mufreq"][:ns], mut["depth_ratio"][:ns], 0.7, 2.4, 1.0,
@@ -724,6 +736,11 @@ def run_other(args, env, local_rank):
                              "api": "sequenza_b200.mufreq_bayes -> sqz_mufreq_point_scalar "
                                     "(pageable numpy arrays in and out)"},
                         gpu_launches=3 * steps,
+                        e2e_pinned_zero_copy={
+                            "value": n / (ms_pin * 1e-3), "unit": "positions/s",
+                            "ms_per_step": ms_pin, "equals_host_api_result": pin_ok,
+                            "api": "sqz_mufreq_point_scalar_dev on pinned host vectors (inputs "
+                                   "read and result written over PCIe by the kernel)"},
                         roofline={"bound": "hbm",
                                   "kernel": "mufreq_lookup_smem_kernel (+ scores and table "
                                             "kernels: two small launches)",
