@@ -55,6 +55,17 @@ namespace {
 constexpr int kPreSeg = 256;  // segments per pre-pass CTA
 }  // namespace
 
+// sqrt(wub) as the grid kernel stores it for CNt 0..7.  The grid kernel turns the high word
+// of this number into a float with one integer instruction, which is right for [1, 2^128)
+// and for +Inf / NaN (they wrap to a small float: a bound that is too low, which is safe);
+// wub >= 1 always (the priors are normalised, R/bayes.R:59).  A factor of 2^128 and more
+// (a BAF residual of 1e38 standard deviations) is stored as +Inf: the copy number can then
+// only be chosen if every other is infinite too, and that grid point is flagged and repaired.
+__device__ __forceinline__ double cw_sqrt_for_float(double wub) {
+  const double r = sqrt(wub);
+  return r < 0x1p128 ? r : __longlong_as_double(0x7FF0000000000000LL);
+}
+
 // ---- pre-pass: BAF factor per (column group, segment, copy number, column) --------------
 // Same arithmetic as baf_colterm_kernel (sqz_baf_split.cu); a short row scan replaces the
 // bracket search (at most 4 rows per copy number for CNt <= 7).
@@ -107,7 +118,7 @@ baf_colterm_cg_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tota
         }
       }
       const double wub = fma(m0, m0, 1.0) * m.w[c];
-      out[c * 32] = store_sqrt ? sqrt(wub) : wub;
+      out[c * 32] = store_sqrt ? cw_sqrt_for_float(wub) : wub;
     }
   }
 }
@@ -153,7 +164,7 @@ baf_colterm_cg8_kernel(BafGridArgs a, CnModel m, int ic0, int nCb, int64_t N_tot
         const double x0 = fma(mb[t], bk.x, bk.y);
         if (fabs(x0) < fabs(m0)) m0 = x0;
       }
-      out[c * 32] = sqrt(fma(m0, m0, 1.0) * w[c]);
+      out[c * 32] = cw_sqrt_for_float(fma(m0, m0, 1.0) * w[c]);
     }
   }
 }
@@ -336,8 +347,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     if (F32) {
       // CNt 0..7: in fp32 and never above the fp64 value.  The midpoint residual loses its
       // rounding margin (sf), the stored factor is cut to the 20 mantissa bits of its high
-      // word (it is >= 1: the priors are normalised, R/bayes.R:59, so the exponent needs a
-      // cap only at the top), products and sums round down.  A bound that is a little low
+      // word (one multiply-add on the integer pattern; the pre-pass keeps it in the range
+      // where that is right), products and sums round down.  A bound that is a little low
       // costs an evaluation, never a result.  Bit patterns of non-negative floats order as
       // integers.
 #pragma unroll
@@ -347,7 +358,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         for (int g = 0; g < B; ++g) {
           const float t = fmaxf(__fsub_rd(fabsf(fmaf(lmc, kf[g], bf[g])), sf[g]), 0.f);
           const unsigned hi = reinterpret_cast<const unsigned*>(col[g])[c * 64 + 1];
-          const float rv = __uint_as_float(min(hi, 0x47EFFFFFu) * 8u + 0x40000000u);
+          const float rv = __uint_as_float(hi * 8u + 0x40000000u);  // see cw_sqrt_for_float
           float lb;
           if (SQ) {
             const float u = __fmul_rd(rv, t);
@@ -534,16 +545,13 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
       }
       if (nsg > k) analyse(base + k, k, std::integral_constant<int, 1>());
     }
-    // (each lane reads back only what it wrote itself: no warp synchronisation needed);
-    // the parameters of the next segment are loaded while the current one is evaluated
+    // (each lane reads back only what it wrote itself: no warp synchronisation needed; the
+    // record is loaded where it is used -- fetching the next one during the evaluation cost
+    // thirteen instructions per segment in moves and index arithmetic, 3 % of the fit)
     {
-      CwPar cur = load_par(pk);
+      const double* pr = pk;
 #pragma unroll 1
-      for (int sg = 0; sg < nsg; ++sg) {
-        const CwPar nxt = load_par(pk + (sg + 1 < nsg ? sg + 1 : sg) * 4 * 32);
-        evaluate(base + sg, cur);
-        cur = nxt;
-      }
+      for (int sg = 0; sg < nsg; ++sg, pr += 4 * 32) evaluate(base + sg, load_par(pr));
     }
     // Once per stage: the products are renormalised (binary exponent -> integer column)
     // before they can overflow; q >= 1, so they never underflow.  `grown` bounds the
