@@ -19,7 +19,7 @@
 //             the tiles of one (group, chunk) are neighbours in the grid and find each
 //             other's rows in L2.
 //   ring      two stages of 4 (CNt 0..7) or 1 (CNt 0..20) segments; lane 0 fills a stage
-//             with one TMA bulk copy (plus one or two for the segments' ratio terms) and
+//             with one TMA bulk copy (plus one for the segments' ratio terms) and
 //             completion is counted on an mbarrier; the stage is refilled as soon as the
 //             warp has left it.
 //   batch     the segments of a stage are analysed together (bounds, argmin, dynamic loads,
@@ -201,9 +201,8 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   extern __shared__ __align__(16) double sm[];
   const int lane = threadIdx.x, tid = threadIdx.x;
   double* stage = sm;                                                           // [kRing][kSegB][NC][32]
-  double2* rkS = reinterpret_cast<double2*>(stage + kRing * kSegB * kSegDoubles);  // [kRing][kSegB]
-  float4* rfS = reinterpret_cast<float4*>(rkS + kRing * kSegB);                 // [kRing][kSegB]
-  double* lm = reinterpret_cast<double*>(rfS + kRing * kSegB) + lane;          // [NC][32]
+  RkRec* rxS = reinterpret_cast<RkRec*>(stage + kRing * kSegB * kSegDoubles);   // [kRing][kSegB]
+  double* lm = reinterpret_cast<double*>(rxS + kRing * kSegB) + lane;          // [NC][32]
   float* lmf = reinterpret_cast<float*>(lm - lane + NC * 32) + lane;            // [NC][32] (F32)
   int* Ec = reinterpret_cast<int*>(lmf - lane + (F32 ? NC * 32 : 0));           // [PT][32]
   double* pk = reinterpret_cast<double*>(Ec + PT * 32) + lane;                  // [kSegB][4][32]
@@ -258,7 +257,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // fp64 value (see analyse).  hcf: half-width of the tile in -log D plus the rounding the
   // fp32 midpoint residual can carry, per unit of |k|: 2^-22 (|lm| + half-width) covers the
   // conversions of lm, k, b and the fused multiply-add (2^-24 each) with room to spare; the
-  // part that scales with |b| comes with the segment (rk32.z).
+  // part that scales with |b| comes with the segment (rkx.f.z).
   const double hw = fmax(fabs(nld[0]), fabs(nld[PT - 1]));
   float hcf = 0.f;
   if (F32) {
@@ -282,24 +281,20 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // 0 issues.  A stage is requested again only after every lane has left it (the
   // __syncwarp before the call).
   const double* f_src = cwc + cb * kSegDoubles;
-  const double2* f_rk = a.rk + cb;
-  const float4* f_rf = a.rk32 + cb;
+  const RkRec* f_rx = a.rkx + cb;
   int64_t f_left = ce - cb;  // segments not yet requested
   int f_s = 0;
   auto fetch = [&]() {
     if (f_left <= 0) return;
     const unsigned cnt = f_left < kSegB ? (unsigned)f_left : (unsigned)kSegB;
     if (lane == 0) {
-      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(double2) +
-                                                  (F32 ? sizeof(float4) : 0)));
+      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(RkRec)));
       tma_bulk_g2s(stage + f_s * kSegB * kSegDoubles, f_src,
                    cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[f_s]);
-      tma_bulk_g2s(rkS + f_s * kSegB, f_rk, cnt * (unsigned)sizeof(double2), &full[f_s]);
-      if (F32) tma_bulk_g2s(rfS + f_s * kSegB, f_rf, cnt * (unsigned)sizeof(float4), &full[f_s]);
+      tma_bulk_g2s(rxS + f_s * kSegB, f_rx, cnt * (unsigned)sizeof(RkRec), &full[f_s]);
     }
     f_src += kSegB * kSegDoubles;
-    f_rk += kSegB;
-    f_rf += kSegB;
+    f_rx += kSegB;
     f_left -= kSegB;
     f_s ^= 1;
   };
@@ -331,9 +326,9 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
     float kf[B], bf[B], sf[B];
 #pragma unroll
     for (int g = 0; g < B; ++g) {
-      rk[g] = rkS[base + g];
+      rk[g] = rxS[base + g].rk;
       if (F32) {
-        const float4 rf = rfS[base + g];
+        const float4 rf = rxS[base + g].f;
         kf[g] = rf.x;
         bf[g] = rf.y;
         // what |x_mid| may lose: the half-width of the tile and the rounding
@@ -469,7 +464,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
         P[j] *= fma(x, x, sg.w1);
       }
     } else {
-      const double2 rk = rkS[slot];
+      const double2 rk = rxS[slot].rk;
       const double* col = stage + slot * kSegDoubles + lane;
       unsigned need = sg.need;
       // a lane with no further candidate repeats its first one: the minimum is unchanged
@@ -602,7 +597,7 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
 static size_t colwarp_smem_bytes(int NC, int PT, int segb, bool f32) {
   const int ring = 2;
   return (size_t)ring * segb * NC * 32 * sizeof(double) +
-         ring * segb * (sizeof(double2) + sizeof(float4)) +
+         ring * segb * sizeof(RkRec) +
          (size_t)NC * 32 * (sizeof(double) + (f32 ? sizeof(float) : 0)) +
          (size_t)PT * 32 * sizeof(int) +
          (size_t)segb * 32 * 4 * sizeof(double);

@@ -34,7 +34,7 @@
 namespace sqz {
 
 // ---- per-segment preparation for the fast path ------------------------------------
-__global__ void baf_prep_kernel(BafGridArgs a, double2* rk, float4* rk32, double2* bk, int* nB) {
+__global__ void baf_prep_kernel(BafGridArgs a, double2* rk, RkRec* rkx, double2* bk, int* nB) {
   const int64_t smp = blockIdx.y;
   const int64_t s0 = a.seg_off[smp], s1 = a.seg_off[smp + 1];
   const double inv_sqrt5 = 0.44721359549995793928;
@@ -55,7 +55,10 @@ __global__ void baf_prep_kernel(BafGridArgs a, double2* rk, float4* rk32, double
     rk[s] = make_double2(kr, -(lr * kr));
     {
       const float kf = __double2float_rn(kr), ef = __double2float_rn(-(lr * kr));
-      rk32[s] = make_float4(kf, ef, __fmul_ru(fabsf(ef), 0x1p-22f), 0.f);
+      RkRec r;
+      r.rk = make_double2(kr, -(lr * kr));
+      r.f = make_float4(kf, ef, __fmul_ru(fabsf(ef), 0x1p-22f), 0.f);
+      rkx[s] = r;
     }
     bk[s] = make_double2(kb, eb);
     cnt += hasB ? 1 : 0;
@@ -828,7 +831,7 @@ static int64_t samples_per_batch(int64_t S, int64_t nP, int64_t nCs) {
 
 struct Workspace {
   double2 *rk, *bk;
-  float4* rk32;
+  RkRec* rkx;
   int* nB;
   double *ploidy, *cell;
   double* partM;
@@ -855,7 +858,7 @@ static Workspace carve(void* base, int64_t N_total, int64_t S, int64_t nP, int64
   const int64_t want = max_chunks(N_total, S);
   w.rk = (double2*)take(n * sizeof(double2));
   w.bk = (double2*)take(n * sizeof(double2));
-  w.rk32 = (float4*)take(n * sizeof(float4));
+  w.rkx = (RkRec*)take(n * sizeof(RkRec));
   w.nB = (int*)take((size_t)(S > 0 ? S : 1) * sizeof(int));
   w.ploidy = (double*)take((size_t)(nP > 0 ? nP : 1) * sizeof(double));
   w.cell = (double*)take((size_t)(nCs > 0 ? nCs : 1) * sizeof(double));
@@ -1035,7 +1038,7 @@ static int baf_grid_core(int64_t S, const int64_t* d_seg_off, int64_t N_total,
   a.wBf = d_wBf;
   a.wr = d_wr;
   a.rk = w.rk;
-  a.rk32 = w.rk32;
+  a.rkx = w.rkx;
   a.bk = w.bk;
   a.ploidy = w.ploidy;
   a.cell = w.cell;
@@ -1076,7 +1079,7 @@ static int baf_grid_core(int64_t S, const int64_t* d_seg_off, int64_t N_total,
       ap.S = sb - sa;
       ap.seg_off = d_seg_off + sa;
       dim3 grid(bx, (unsigned)(sb - sa));
-      baf_prep_kernel<<<grid, 256, 0, st>>>(ap, w.rk, w.rk32, w.bk, w.nB + sa);
+      baf_prep_kernel<<<grid, 256, 0, st>>>(ap, w.rk, w.rkx, w.bk, w.nB + sa);
       SQZ_CUDA(cudaGetLastError());
       ++launches;
     }

@@ -19,13 +19,19 @@ namespace sqz {
 
 constexpr int kMaxOut = 8;  // destinations of one result (this GPU and its peers)
 
+struct alignas(32) RkRec {
+  double2 rk;
+  float4 f;  // (float)kr, (float)er, 2^-22 |er| rounded up, unused
+};
+
 struct BafGridArgs {
   int64_t S;
   const int64_t* seg_off;  // [S+1]
   const double *Bf, *ratio, *sdBf, *sdr, *wBf, *wr;  // raw per-segment vectors
   const double2* rk;  // fast path: (kr, er)   xr/sqrt5 = fma(log mr, kr, er)
-  // (kr, er) as floats and 2^-22 |er| rounded up: fp32 bounds of the column-per-lane kernel
-  const float4* rk32;
+  // the same with (kr, er) as floats and 2^-22 |er| rounded up behind it (the fp32 bounds of
+  // the column-per-lane kernel): one 32-byte record per segment, one bulk copy per stage
+  const RkRec* rkx;
   const double2* bk;  // fast path: (kb, eb)   xb/sqrt5 = fma(mb, kb, eb)
   const int* nB;      // [S] segments that carry a BAF term
   const double* adr;  // [S] avg.depth.ratio
