@@ -282,21 +282,26 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   // __syncwarp before the call).
   const double* f_src = cwc + cb * kSegDoubles;
   const RkRec* f_rx = a.rkx + cb;
-  int64_t f_left = ce - cb;  // segments not yet requested
-  int f_s = 0;
+  int f_left = (int)(ce > cb ? ce - cb : 0);  // segments not yet requested
+  unsigned f_s = 0;
+  // (shared-memory addresses in the 32-bit window, converted once)
+  const unsigned stage_a = smem_u32(stage), rx_a = smem_u32(rxS), full_a = smem_u32(full);
+  constexpr unsigned kStageBytes = kSegB * kSegDoubles * sizeof(double);
   auto fetch = [&]() {
     if (f_left <= 0) return;
     const unsigned cnt = f_left < kSegB ? (unsigned)f_left : (unsigned)kSegB;
     if (lane == 0) {
-      mbar_expect_tx(&full[f_s], cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(RkRec)));
-      tma_bulk_g2s(stage + f_s * kSegB * kSegDoubles, f_src,
-                   cnt * (unsigned)(kSegDoubles * sizeof(double)), &full[f_s]);
-      tma_bulk_g2s(rxS + f_s * kSegB, f_rx, cnt * (unsigned)sizeof(RkRec), &full[f_s]);
+      const unsigned bar = full_a + f_s * 8u;
+      mbar_expect_tx_a(bar, cnt * (unsigned)(kSegDoubles * sizeof(double) + sizeof(RkRec)));
+      tma_bulk_g2s_a(stage_a + f_s * kStageBytes, f_src,
+                     cnt * (unsigned)(kSegDoubles * sizeof(double)), bar);
+      tma_bulk_g2s_a(rx_a + f_s * (unsigned)(kSegB * sizeof(RkRec)), f_rx,
+                     cnt * (unsigned)sizeof(RkRec), bar);
     }
     f_src += kSegB * kSegDoubles;
     f_rx += kSegB;
     f_left -= kSegB;
-    f_s ^= 1;
+    f_s ^= 1u;
   };
 
   double P[PT];
@@ -524,12 +529,12 @@ baf_grid_colwarp_kernel(BafGridArgs a, CnModel m, const double* __restrict__ cwg
   int s = 0;
   unsigned phase = 0;
 #pragma unroll 1
-  for (int64_t left = ce - cb; left > 0; left -= kSegB) {
+  for (int left = (int)(ce > cb ? ce - cb : 0); left > 0; left -= kSegB) {
     __syncwarp();
     fetch();  // the stage left in the previous round is requested again
-    mbar_wait(&full[s], phase);
+    mbar_wait_a(full_a + (unsigned)s * 8u, phase);
     const int base = s * kSegB;
-    const int nsg = left < kSegB ? (int)left : kSegB;
+    const int nsg = left < kSegB ? left : kSegB;
     if (nsg == kSegB) {
       analyse(base, 0, std::integral_constant<int, kSegB>());
     } else {  // ragged last stage of the chunk
